@@ -1,0 +1,203 @@
+// gsr_api.cu -- the extern "C" boundary declared in include/gsr.h and the stage orchestration that
+// replaces CudaRasterizer::Rasterizer::forward / backward (rasterizer_impl.cu:198-336, 340-434).
+#include "gsr_common.cuh"
+#include <cstdio>
+#include <cstring>
+
+namespace gsr {
+
+unsigned long long g_launches = 0;
+
+int check_launch(const char* what, bool debug, cudaStream_t s) {
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess && debug) {            // auxiliary.h:166-173 (CHECK_CUDA in debug mode)
+        e = cudaStreamSynchronize(s);
+        if (e == cudaSuccess) e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) {
+        fprintf(stderr, "\n[GSR CUDA ERROR] %s: %s\n", what, cudaGetErrorString(e));
+        return (int)e;
+    }
+    return 0;
+}
+
+static size_t blob_size_geom(size_t P) {
+    char* p = nullptr;
+    GeomState::from(p, P);
+    return (size_t)p + GSR_ALIGN;
+}
+static size_t blob_size_binning(size_t R) {
+    char* p = nullptr;
+    BinningState::from(p, R);
+    return (size_t)p + GSR_ALIGN;
+}
+static size_t blob_size_image(size_t N, size_t tiles) {
+    char* p = nullptr;
+    ImageState::from(p, N, tiles);
+    return (size_t)p + GSR_ALIGN;
+}
+static inline int tiles_of(int W, int H) { return ((W + GSR_TILE - 1) / GSR_TILE) * ((H + GSR_TILE - 1) / GSR_TILE); }
+
+static bool view_ok(const gsr_view* v) {
+    if (!v || v->P < 0 || v->W <= 0 || v->H <= 0) return false;
+    if (v->P == 0) return true;
+    if (!v->means3D || !v->opacities || !v->viewmatrix || !v->projmatrix || !v->background) return false;
+    if (!v->shs && !v->colors_precomp) return false;
+    if (v->shs && (!v->cam_pos || v->M < (v->D + 1) * (v->D + 1) || v->D < 0 || v->D > 3)) return false;
+    if (!v->cov3D_precomp && (!v->scales || !v->rotations)) return false;
+    return true;
+}
+
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" {
+
+size_t gsr_required_geom(int P) { return blob_size_geom((size_t)(P > 0 ? P : 0)); }
+size_t gsr_required_binning(int R, int W, int H) { (void)W; (void)H; return blob_size_binning((size_t)(R > 0 ? R : 0)); }
+size_t gsr_required_image(int W, int H) { return blob_size_image((size_t)W * H, (size_t)tiles_of(W, H)); }
+int gsr_key_bits(int W, int H) { return 32 + (int)higher_msb((uint32_t)tiles_of(W, H)); }
+size_t gsr_backward_scratch_bytes(int P) { return sizeof(float) * GSR_ACC_FLOATS * (size_t)(P > 0 ? P : 0) + 256; }
+size_t gsr_dist2_temp_bytes(int P) { return dist2_temp_bytes(P); }
+uint64_t gsr_launch_count(void) { return g_launches; }
+const char* gsr_version(void) { return "gsr 0.1 (sm_100a)"; }
+
+const char* gsr_error_string(int code) {
+    switch (code) {
+        case 0: return "ok";
+        case GSR_E_BADARG: return "gsr: bad argument";
+        case GSR_E_TOOLARGE: return "gsr: num_rendered too large";
+        case GSR_E_ALLOC: return "gsr: scratch allocation callback returned NULL";
+        default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "gsr: unknown error";
+    }
+}
+
+int gsr_geom_layout(int P, size_t* off, int max_off) {
+    char* p = nullptr;
+    GeomState g = GeomState::from(p, (size_t)P);
+    const size_t v[] = {(size_t)g.depths, (size_t)g.rec, (size_t)g.clamped, (size_t)g.tiles_touched,
+                        (size_t)g.point_offsets, (size_t)g.order, (size_t)g.dkey};
+    int n = 0;
+    for (; n < (int)(sizeof(v) / sizeof(v[0])) && n < max_off; n++) off[n] = v[n];
+    return n;
+}
+int gsr_binning_layout(int R, int W, int H, size_t* off, int max_off) {
+    (void)W; (void)H;
+    char* p = nullptr;
+    BinningState b = BinningState::from(p, (size_t)R);
+    const size_t v[] = {(size_t)b.tile_keys, (size_t)b.point_list, (size_t)b.tile_keys_tmp, (size_t)b.vals_tmp};
+    int n = 0;
+    for (; n < 4 && n < max_off; n++) off[n] = v[n];
+    return n;
+}
+int gsr_image_layout(int W, int H, size_t* off, int max_off) {
+    char* p = nullptr;
+    ImageState s = ImageState::from(p, (size_t)W * H, (size_t)tiles_of(W, H));
+    const size_t v[] = {(size_t)s.final_T, (size_t)s.n_contrib, (size_t)s.ranges};
+    int n = 0;
+    for (; n < 3 && n < max_off; n++) off[n] = v[n];
+    return n;
+}
+
+int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, gsr_alloc_fn binning_alloc,
+                void* binning_ctx, gsr_alloc_fn image_alloc, void* image_ctx, float* out_color, int* radii,
+                float* out_invdepth, int* num_rendered, void* stream) {
+    if (!view_ok(view) || !geom_alloc || !binning_alloc || !image_alloc || !out_color || !num_rendered) return GSR_E_BADARG;
+    const gsr_view& v = *view;
+    cudaStream_t s = (cudaStream_t)stream;
+    *num_rendered = 0;
+    const size_t N = (size_t)v.W * v.H;
+    const int tiles = tiles_of(v.W, v.H);
+    if (v.P == 0) {   // rasterize_points.cu:81 : outputs stay zero-filled
+        cudaError_t e = cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * N, s);
+        if (e == cudaSuccess && out_invdepth) e = cudaMemsetAsync(out_invdepth, 0, sizeof(float) * N, s);
+        return (int)e;
+    }
+    if (!radii) return GSR_E_BADARG;
+    char* gp = geom_alloc(geom_ctx, blob_size_geom((size_t)v.P));
+    char* ip = image_alloc(image_ctx, blob_size_image(N, (size_t)tiles));
+    if (!gp || !ip) return GSR_E_ALLOC;
+    GeomState g = GeomState::from(gp, (size_t)v.P);
+    ImageState img = ImageState::from(ip, N, (size_t)tiles);
+
+    int e = launch_preprocess(v, g, radii, s);
+    if (e) return e;
+    uint32_t* total_dev = nullptr;
+    e = launch_order_and_scan(v, g, &total_dev, s);
+    if (e) return e;
+    uint32_t R = 0;   // rasterizer_impl.cu:281 : the one host synchronisation of the forward
+    cudaError_t ce = cudaMemcpyAsync(&R, total_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, s);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    if (ce != cudaSuccess) return (int)ce;
+    if (R >= (1u << 30)) return GSR_E_TOOLARGE;
+    *num_rendered = (int)R;
+    char* bp = binning_alloc(binning_ctx, blob_size_binning((size_t)R));
+    if (!bp) return GSR_E_ALLOC;
+    BinningState b = BinningState::from(bp, (size_t)R);
+    e = launch_binning(v, g, radii, b, img, (int)R, s);
+    if (e) return e;
+    return launch_blend_forward(v, g, b, img, out_color, out_invdepth, s);
+}
+
+int gsr_backward(const gsr_view* view, int R, const int* radii, const char* geom, const char* binning, const char* image,
+                 const float* dL_dpix, const float* dL_dinvdepth, char* accum_scratch, const gsr_grads* out, void* stream) {
+    if (!view_ok(view) || !out) return GSR_E_BADARG;
+    const gsr_view& v = *view;
+    if (v.P == 0) return 0;
+    if (!radii || !geom || !image || !dL_dpix || !accum_scratch || !out->dL_dmeans2D || !out->dL_dopacity ||
+        !out->dL_dmeans3D || (R > 0 && !binning))
+        return GSR_E_BADARG;
+    if (v.shs && !out->dL_dsh) return GSR_E_BADARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    char* gp = const_cast<char*>(geom);
+    char* ip = const_cast<char*>(image);
+    GeomState g = GeomState::from(gp, (size_t)v.P);
+    ImageState img = ImageState::from(ip, (size_t)v.W * v.H, (size_t)tiles_of(v.W, v.H));
+    BinningState b;
+    memset(&b, 0, sizeof(b));
+    if (R > 0) {
+        char* bp = const_cast<char*>(binning);
+        b = BinningState::from(bp, (size_t)R);
+    }
+    char* ap = accum_scratch;
+    float* acc = carve<float>(ap, (size_t)v.P * GSR_ACC_FLOATS);
+    cudaError_t ce = cudaMemsetAsync(acc, 0, sizeof(float) * GSR_ACC_FLOATS * (size_t)v.P, s);
+    if (ce != cudaSuccess) return (int)ce;
+    int e = 0;
+    if (R > 0) {
+        e = launch_blend_backward(v, g, b, img, dL_dpix, dL_dinvdepth, acc, s);
+        if (e) return e;
+    }
+    gsr_grads o = *out;
+    if (!v.shs) o.dL_dsh = nullptr;
+    if (!v.scales) { o.dL_dscales = nullptr; o.dL_drotations = nullptr; }
+    return launch_preprocess_backward(v, g, radii, acc, dL_dinvdepth != nullptr, o, s);
+}
+
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,
+                     void* stream) {
+    (void)projmatrix;   // the reference computes p_proj but never uses it (auxiliary.h:149-151)
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return GSR_E_BADARG;
+    if (P == 0) return 0;
+    return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
+}
+
+int gsr_dist2(int P, const float* points_xyz, float* mean_d2, char* temp, void* stream) {
+    if (P < 0 || (P > 0 && (!points_xyz || !mean_d2 || !temp))) return GSR_E_BADARG;
+    return launch_dist2(P, points_xyz, mean_d2, temp, (cudaStream_t)stream);
+}
+
+// Parity helper (not on the hot path): reconstruct the reference's sorted 64-bit keys
+// (tile << 32 | depth bits) for the instances of the last forward, for bit-exact comparison.
+int gsr_debug_sorted_keys(const gsr_view* view, int R, const char* geom, const char* binning, uint64_t* keys_out,
+                          void* stream) {
+    if (!view || !geom || !binning || !keys_out) return GSR_E_BADARG;
+    char* gp = const_cast<char*>(geom);
+    char* bp = const_cast<char*>(binning);
+    GeomState g = GeomState::from(gp, (size_t)view->P);
+    BinningState b = BinningState::from(bp, (size_t)R);
+    return launch_sorted_keys_debug(*view, g, b, R, keys_out, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,140 @@
+// gsr_common.cuh -- shared declarations for the sm_100a rasterizer kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/gsr.h"
+
+#define GSR_TILE 16          // observable contract: tile ids appear in keys / ranges (config.h:16-17)
+#define GSR_ALIGN 128
+
+namespace gsr {
+
+// ---------------------------------------------------------------- launch accounting / checks
+extern unsigned long long g_launches;
+int check_launch(const char* what, bool debug, cudaStream_t s);
+#define GSR_LAUNCH(what, debug, stream, ...)                 \
+    do {                                                     \
+        __VA_ARGS__;                                         \
+        gsr::g_launches++;                                   \
+        int _e = gsr::check_launch(what, debug, stream);     \
+        if (_e) return _e;                                   \
+    } while (0)
+
+// ---------------------------------------------------------------- scratch layouts (private)
+template <typename T>
+static inline T* carve(char*& p, size_t count) {
+    uintptr_t a = (reinterpret_cast<uintptr_t>(p) + GSR_ALIGN - 1) & ~uintptr_t(GSR_ALIGN - 1);
+    T* r = reinterpret_cast<T*>(a);
+    p = reinterpret_cast<char*>(r + count);
+    return r;
+}
+
+#define GSR_SORT_TILE 4096    // keys per radix-sort tile (256 threads x 16)
+#define GSR_RADIX 256
+#define GSR_SCAN_TILE 2048    // items per scan tile (256 threads x 8)
+
+static inline size_t sort_tiles(size_t n) { return (n + GSR_SORT_TILE - 1) / GSR_SORT_TILE; }
+// scratch words for radix_sort_u32 over n items: per-pass digit totals + the [256][tiles] table
+static inline size_t sort_scratch_words(size_t n) { return 8 * GSR_RADIX + GSR_RADIX * sort_tiles(n) + 64; }
+
+struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46)
+    float* depths;            // [P] view-space z (visible Gaussians only)
+    float4* rec;              // [3P] splat records: {x,y,ex,ey} {a,b,c,opacity} {r,g,b,1/depth}
+    uint8_t* clamped;         // [P] bit c set = channel c clamped at 0
+    uint32_t* tiles_touched;  // [P]
+    uint32_t* dkey;           // [P] depth bits (0xFFFFFFFF for culled Gaussians): Gaussian-level sort key
+    uint32_t* dkey_tmp;       // [P]
+    uint32_t* order;          // [P] Gaussian ids in (depth, id) order
+    uint32_t* order_tmp;      // [P]
+    uint32_t* point_offsets;  // [P] inclusive scan of tiles_touched[order[j]]  (depth order!)
+    uint32_t* scan_sums;      // [scan tiles + 8]; last word = total (num_rendered)
+    uint32_t* sort_scratch;   // radix-sort tables for the P-sized sort
+    static GeomState from(char*& p, size_t P) {
+        GeomState g;
+        g.depths = carve<float>(p, P);
+        g.rec = carve<float4>(p, 3 * P);
+        g.clamped = carve<uint8_t>(p, P);
+        g.tiles_touched = carve<uint32_t>(p, P);
+        g.dkey = carve<uint32_t>(p, P);
+        g.dkey_tmp = carve<uint32_t>(p, P);
+        g.order = carve<uint32_t>(p, P);
+        g.order_tmp = carve<uint32_t>(p, P);
+        g.point_offsets = carve<uint32_t>(p, P);
+        g.scan_sums = carve<uint32_t>(p, (P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE + 8);
+        g.sort_scratch = carve<uint32_t>(p, sort_scratch_words(P));
+        return g;
+    }
+};
+
+struct ImageState {           // replaces ImageState (rasterizer_impl.h:48-55)
+    float* final_T;           // [N]
+    uint32_t* n_contrib;      // [N]
+    uint2* ranges;            // [tiles]
+    static ImageState from(char*& p, size_t N, size_t tiles) {
+        ImageState s;
+        s.final_T = carve<float>(p, N);
+        s.n_contrib = carve<uint32_t>(p, N);
+        s.ranges = carve<uint2>(p, tiles);
+        return s;
+    }
+};
+
+struct BinningState {         // replaces BinningState (rasterizer_impl.h:57-66)
+    uint32_t* tile_keys;      // [R] tile id per instance, sorted (final)
+    uint32_t* point_list;     // [R] Gaussian ids sorted by (tile, depth, id) (final)
+    uint32_t* tile_keys_tmp;  // [R]
+    uint32_t* vals_tmp;       // [R]
+    uint32_t* sort_scratch;   // radix-sort tables for the R-sized sort
+    static BinningState from(char*& p, size_t R) {
+        BinningState b;
+        size_t Rp = R + 8;
+        b.tile_keys = carve<uint32_t>(p, Rp);
+        b.point_list = carve<uint32_t>(p, Rp);
+        b.tile_keys_tmp = carve<uint32_t>(p, Rp);
+        b.vals_tmp = carve<uint32_t>(p, Rp);
+        b.sort_scratch = carve<uint32_t>(p, sort_scratch_words(R));
+        return b;
+    }
+};
+
+static inline uint32_t higher_msb(uint32_t n) {   // rasterizer_impl.cu:35-50
+    uint32_t msb = sizeof(n) * 4, step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step; else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+// Packed per-Gaussian gradient accumulator written by the backward blend (12 floats = 3 x float4):
+//   [0] dmean2D.x  [1] dmean2D.y  [2] dconic.xx  [3] dconic.xy
+//   [4] dconic.yy  [5] dopacity   [6] dcolor.r   [7] dcolor.g
+//   [8] dcolor.b   [9] dinvdepth  [10],[11] unused
+#define GSR_ACC_FLOATS 12
+
+// ---------------------------------------------------------------- stage entry points (host)
+int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s);
+int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s);
+// depth-order the Gaussians, scan their tile counts in that order; total lands in g.scan_sums (device)
+int launch_order_and_scan(const gsr_view& v, GeomState& g, uint32_t** total_dev, cudaStream_t s);
+int launch_binning(const gsr_view& v, const GeomState& g, const int* radii, BinningState& b, ImageState& img,
+                   int R, cudaStream_t s);
+int launch_blend_forward(const gsr_view& v, const GeomState& g, const BinningState& b, ImageState& img,
+                         float* out_color, float* out_invdepth, cudaStream_t s);
+int launch_blend_backward(const gsr_view& v, const GeomState& g, const BinningState& b, const ImageState& img,
+                          const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s);
+int launch_preprocess_backward(const gsr_view& v, const GeomState& g, const int* radii, const float* acc,
+                               bool have_invdepth, const gsr_grads& out, cudaStream_t s);
+// Stable LSD radix sort of (u32 key, u32 value) pairs on key bits [0, total_bits). Ping-pongs between
+// (ka,va) and (kb,vb); *result_in_a tells where the sorted data ended up. scratch: sort_scratch_words(n).
+int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits,
+                   uint32_t* scratch, bool* result_in_a, bool debug, cudaStream_t s);
+static inline int radix_passes(int total_bits) { return (total_bits + 7) / 8; }
+int launch_sorted_keys_debug(const gsr_view& v, const GeomState& g, const BinningState& b, int R, uint64_t* keys_out,
+                             cudaStream_t s);
+int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s);
+size_t dist2_temp_bytes(int P);
+
+}  // namespace gsr

@@ -1,0 +1,266 @@
+"""ctypes binding of libgsr.so with the call shapes of the reference's pybind module `_C`
+(submodules/diff-gaussian-rasterization/rasterize_points.cu:35-217, ext.cpp:15-19).
+
+torch is used for device memory and the current stream only; every computation happens in the
+hand-written sm_100a kernels behind include/gsr.h. There is NO fallback: if libgsr.so is missing or a
+tensor is not on a CUDA device, this raises.
+"""
+import ctypes as C
+import os
+import torch
+
+_PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_LIB_PATH = os.path.join(_PKG_ROOT, "libgsr.so")
+
+
+class _View(C.Structure):
+    _fields_ = [("P", C.c_int), ("D", C.c_int), ("M", C.c_int), ("W", C.c_int), ("H", C.c_int),
+                ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
+                ("prefiltered", C.c_int), ("antialiasing", C.c_int), ("debug", C.c_int)] + \
+               [(n, C.c_void_p) for n in ("background", "means3D", "shs", "colors_precomp", "opacities", "scales",
+                                          "rotations", "cov3D_precomp", "viewmatrix", "projmatrix", "cam_pos")]
+
+
+class _Grads(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("dL_dmeans2D", "dL_dopacity", "dL_dmeans3D", "dL_dcolors", "dL_dcov3D",
+                                          "dL_dsh", "dL_dscales", "dL_drotations", "dL_dconic")]
+
+
+_ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
+_lib = None
+
+
+def lib():
+    """Loads libgsr.so once. Fails loudly when the CUDA library has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise ImportError(f"{_LIB_PATH} not found: build it with `python gaussian-splatting-slam_b200/build.py` "
+                              "(there is no CPU or PyTorch fallback for the rasterizer)")
+        L = C.CDLL(_LIB_PATH)
+        L.gsr_forward.restype = C.c_int
+        L.gsr_forward.argtypes = [C.POINTER(_View), _ALLOC_FN, C.c_void_p, _ALLOC_FN, C.c_void_p, _ALLOC_FN, C.c_void_p,
+                                  C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.c_void_p]
+        L.gsr_backward.restype = C.c_int
+        L.gsr_backward.argtypes = [C.POINTER(_View), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p, C.POINTER(_Grads), C.c_void_p]
+        L.gsr_mark_visible.restype = C.c_int
+        L.gsr_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.gsr_dist2.restype = C.c_int
+        L.gsr_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.gsr_debug_sorted_keys.restype = C.c_int
+        L.gsr_debug_sorted_keys.argtypes = [C.POINTER(_View), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        for n in ("gsr_required_geom", "gsr_required_image", "gsr_backward_scratch_bytes", "gsr_dist2_temp_bytes"):
+            getattr(L, n).restype = C.c_size_t
+        L.gsr_required_binning.restype = C.c_size_t
+        L.gsr_launch_count.restype = C.c_uint64
+        L.gsr_error_string.restype = C.c_char_p
+        L.gsr_version.restype = C.c_char_p
+        for n in ("gsr_geom_layout", "gsr_image_layout"):
+            getattr(L, n).restype = C.c_int
+        L.gsr_binning_layout.restype = C.c_int
+        _lib = L
+    return _lib
+
+
+def _check(code, what):
+    if code != 0:
+        raise RuntimeError(f"{what}: {lib().gsr_error_string(code).decode()} (code {code})")
+
+
+def _dev(t, name):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (the rasterizer has no CPU path)")
+    return t
+
+
+def _f32(t):
+    """contiguous fp32 view of t (rasterize_points.cu:94-111 calls .contiguous() on every input)."""
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _ptr(t):
+    return None if t is None or t.numel() == 0 else t.data_ptr()
+
+
+class _Scratch:
+    """The three resizable byte buffers of rasterize_points.cu:68-78, handed out through callbacks."""
+
+    def __init__(self, device):
+        self.device = device
+        self.bufs = {}
+        self.err = None
+
+        def make(key):
+            def cb(_ctx, nbytes):
+                try:
+                    t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+                    self.bufs[key] = t
+                    return t.data_ptr()
+                except Exception as ex:   # surfaces as GSR_E_ALLOC, re-raised by the caller
+                    self.err = ex
+                    return 0
+            return _ALLOC_FN(cb)
+        self.cbs = [make(k) for k in ("geom", "binning", "image")]
+
+    def get(self, key):
+        t = self.bufs.get(key)
+        return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
+
+
+def _make_view(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+               projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug, antialiasing, keep):
+    M = sh.size(1) if sh.numel() != 0 else 0          # rasterize_points.cu:84-88
+    ts = dict(background=bg, means3D=means3D, shs=sh, colors_precomp=colors, opacities=opacity, scales=scales,
+              rotations=rotations, cov3D_precomp=cov3D_precomp, viewmatrix=viewmatrix, projmatrix=projmatrix,
+              cam_pos=campos)
+    ptrs = {}
+    for k, t in ts.items():
+        if t is None or t.numel() == 0:
+            ptrs[k] = None
+        else:
+            t = _f32(_dev(t, k))
+            keep.append(t)
+            ptrs[k] = t.data_ptr()
+    return _View(int(means3D.size(0)), int(degree), int(M), int(W), int(H), float(tan_fovx), float(tan_fovy),
+                 float(scale_modifier), int(bool(prefiltered)), int(bool(antialiasing)), int(bool(debug)),
+                 ptrs["background"], ptrs["means3D"], ptrs["shs"], ptrs["colors_precomp"], ptrs["opacities"],
+                 ptrs["scales"], ptrs["rotations"], ptrs["cov3D_precomp"], ptrs["viewmatrix"], ptrs["projmatrix"],
+                 ptrs["cam_pos"])
+
+
+def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                        projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
+                        debug, antialiasing=False, want_invdepth=True):
+    """rasterize_points.cu:35-115 + superset outputs. Returns
+    (num_rendered, color[3,H,W], radii[P] int32, geomBuffer, binningBuffer, imgBuffer, invdepth[1,H,W])."""
+    if means3D.ndim != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")   # rasterize_points.cu:57-59
+    _dev(means3D, "means3D")
+    H, W, P = int(image_height), int(image_width), int(means3D.size(0))
+    dev = means3D.device
+    with torch.cuda.device(dev):
+        keep = []
+        view = _make_view(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                          projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug, antialiasing, keep)
+        color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
+        scratch = _Scratch(dev)
+        n = C.c_int(0)
+        rc = lib().gsr_forward(C.byref(view), scratch.cbs[0], None, scratch.cbs[1], None, scratch.cbs[2], None,
+                               color.data_ptr(), _ptr(radii), _ptr(invdepth), C.byref(n),
+                               torch.cuda.current_stream(dev).cuda_stream)
+        if scratch.err is not None:
+            raise scratch.err
+        _check(rc, "gsr_forward")
+    return n.value, color, radii, scratch.get("geom"), scratch.get("binning"), scratch.get("image"), invdepth
+
+
+def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                                 viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
+                                 degree, campos, geomBuffer, R, binningBuffer, imageBuffer, antialiasing, debug,
+                                 want_conic=False):
+    """rasterize_points.cu:117-196. Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
+    dL_dscales, dL_drotations); gradients of inputs that were not supplied are None. With want_conic=True a 9th
+    tensor dL_dconic[P,2,2] is appended (parity tests)."""
+    P = int(means3D.size(0))
+    H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    dev = means3D.device
+    with torch.cuda.device(dev):
+        keep = []
+        view = _make_view(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                          projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, False, debug, antialiasing, keep)
+        M = view.M
+        f = dict(dtype=torch.float32, device=dev)
+        dL_dmeans3D = torch.empty((P, 3), **f)
+        dL_dmeans2D = torch.empty((P, 3), **f)
+        dL_dopacity = torch.empty((P, 1), **f)
+        dL_dcolors = torch.empty((P, 3), **f) if colors.numel() != 0 else None
+        dL_dcov3D = torch.empty((P, 6), **f) if cov3D_precomp.numel() != 0 else None
+        dL_dsh = torch.empty((P, M, 3), **f) if sh.numel() != 0 else None
+        dL_dscales = torch.empty((P, 3), **f) if scales.numel() != 0 else None
+        dL_drot = torch.empty((P, 4), **f) if rotations.numel() != 0 else None
+        dL_dconic = torch.empty((P, 2, 2), **f) if want_conic else None
+        if P != 0:
+            g = _Grads(_ptr(dL_dmeans2D), _ptr(dL_dopacity), _ptr(dL_dmeans3D), _ptr(dL_dcolors), _ptr(dL_dcov3D),
+                       _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot), _ptr(dL_dconic))
+            dpix = _f32(dL_dout_color)
+            dinv = _f32(dL_dout_invdepth) if dL_dout_invdepth is not None else None
+            acc = torch.empty(int(lib().gsr_backward_scratch_bytes(P)), dtype=torch.uint8, device=dev)
+            rc = lib().gsr_backward(C.byref(view), int(R), _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
+                                    _ptr(imageBuffer), dpix.data_ptr(), _ptr(dinv), acc.data_ptr(), C.byref(g),
+                                    torch.cuda.current_stream(dev).cuda_stream)
+            _check(rc, "gsr_backward")
+    out = (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drot)
+    return out + (dL_dconic,) if want_conic else out
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """rasterize_points.cu:198-217"""
+    _dev(means3D, "means3D")
+    P = int(means3D.size(0))
+    dev = means3D.device
+    present = torch.zeros((P,), dtype=torch.bool, device=dev)
+    if P != 0:
+        with torch.cuda.device(dev):
+            m, v, p = _f32(means3D), _f32(_dev(viewmatrix, "viewmatrix")), _f32(_dev(projmatrix, "projmatrix"))
+            _check(lib().gsr_mark_visible(P, m.data_ptr(), v.data_ptr(), p.data_ptr(), present.data_ptr(),
+                                          torch.cuda.current_stream(dev).cuda_stream), "gsr_mark_visible")
+    return present
+
+
+def launch_count():
+    return int(lib().gsr_launch_count())
+
+
+def decode_state(P, R, W, H, geomBuffer, binningBuffer, imgBuffer, view_args=None):
+    """Parity helper: slices the private scratch blobs into named tensors (layouts from gsr_*_layout)."""
+    L = lib()
+    off = (C.c_size_t * 8)()
+
+    def base(t):
+        return (-t.data_ptr()) % 128
+
+    def take(buf, o, nbytes, dtype, shape):
+        b0 = base(buf)
+        return buf[b0 + o: b0 + o + nbytes].view(dtype).view(*shape)
+    out = {}
+    n = L.gsr_geom_layout(C.c_int(P), off, 8)
+    go = [off[i] for i in range(n)]
+    out["depths"] = take(geomBuffer, go[0], 4 * P, torch.float32, (P,))
+    rec = take(geomBuffer, go[1], 48 * P, torch.float32, (P, 12))
+    out["means2D"], out["extent"] = rec[:, 0:2], rec[:, 2:4]
+    out["conic_opacity"], out["rgb"], out["invdepth_g"] = rec[:, 4:8], rec[:, 8:11], rec[:, 11]
+    out["clamped"] = take(geomBuffer, go[2], P, torch.uint8, (P,))
+    out["tiles_touched"] = take(geomBuffer, go[3], 4 * P, torch.int32, (P,))
+    out["point_offsets"] = take(geomBuffer, go[4], 4 * P, torch.int32, (P,))
+    out["order"] = take(geomBuffer, go[5], 4 * P, torch.int32, (P,))
+    n = L.gsr_image_layout(C.c_int(W), C.c_int(H), off, 8)
+    io = [off[i] for i in range(n)]
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    out["final_T"] = take(imgBuffer, io[0], 4 * W * H, torch.float32, (H * W,))
+    out["n_contrib"] = take(imgBuffer, io[1], 4 * W * H, torch.int32, (H * W,))
+    out["ranges"] = take(imgBuffer, io[2], 8 * tiles, torch.int32, (tiles, 2))
+    if R > 0:
+        n = L.gsr_binning_layout(C.c_int(R), C.c_int(W), C.c_int(H), off, 8)
+        bo = [off[i] for i in range(n)]
+        out["tile_keys"] = take(binningBuffer, bo[0], 4 * R, torch.int32, (R,))
+        out["point_list"] = take(binningBuffer, bo[1], 4 * R, torch.int32, (R,))
+    return out
+
+
+def sorted_keys(P, R, geomBuffer, binningBuffer):
+    """Parity helper: the reference's sorted u64 keys (as int64) for the last forward."""
+    dev = geomBuffer.device
+    keys = torch.empty((R,), dtype=torch.int64, device=dev)
+    if R > 0:
+        view = _View()
+        view.P = P
+        with torch.cuda.device(dev):
+            _check(lib().gsr_debug_sorted_keys(C.byref(view), R, geomBuffer.data_ptr(), binningBuffer.data_ptr(),
+                                               keys.data_ptr(), torch.cuda.current_stream(dev).cuda_stream),
+                   "gsr_debug_sorted_keys")
+    return keys
