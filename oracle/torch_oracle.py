@@ -11,6 +11,8 @@ Reference behaviours reproduced on purpose so that autograd equals backward.cu:
     the clamp)  -> straight-through estimator below.
   * grad of means2D is d/d(NDC-scaled pixel) (backward.cu:460-461,545-546) -> the dummy
     `means2D` input is added in NDC space before ndc2Pix.
+  * the frustum clamp of t.x/t.z, t.y/t.z (forward.cu:84-88) is backpropagated as the reference does: a clamped
+    coordinate is a constant (backward.cu:174-175,258-260 drop the d(lim*t.z)/dt.z term).
   * dL/dscale is taken w.r.t. (scale_modifier*scale) (backward.cu:278-341); compare gradients
     with scale_modifier == 1.
 Citations are relative to submodules/diff-gaussian-rasterization/cuda_rasterizer/.
@@ -88,8 +90,13 @@ def preprocess(means3D, means2D, opacities, shs, colors_precomp, scales, rotatio
     tz = pv[:, 2]
     tz_safe = torch.where(tz.abs() > 1e-12, tz, torch.full_like(tz, 1e-12))
     limx, limy = 1.3 * tanfovx, 1.3 * tanfovy
-    tx = torch.clamp(pv[:, 0] / tz_safe, -limx, limx) * tz
-    ty = torch.clamp(pv[:, 1] / tz_safe, -limy, limy) * tz
+    # backward.cu:168-177,258-260: a clamped t.x / t.y is a CONSTANT for the reference's backward (x_grad_mul = 0
+    # and no d(lim*t.z)/dt.z term); an unclamped one has gradient 1 w.r.t. view-space x / y only.
+    rx, ry = pv[:, 0] / tz_safe, pv[:, 1] / tz_safe
+    in_x = ((rx >= -limx) & (rx <= limx)).to(dt).detach()
+    in_y = ((ry >= -limy) & (ry <= limy)).to(dt).detach()
+    tx = (torch.clamp(rx, -limx, limx) * tz).detach() + (pv[:, 0] - pv[:, 0].detach()) * in_x
+    ty = (torch.clamp(ry, -limy, limy) * tz).detach() + (pv[:, 1] - pv[:, 1].detach()) * in_y
     z0 = torch.zeros_like(tz)
     J = torch.stack([fx / tz_safe, z0, -(fx * tx) / (tz_safe * tz_safe),
                      z0, fy / tz_safe, -(fy * ty) / (tz_safe * tz_safe)], dim=1).view(P, 2, 3)
