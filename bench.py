@@ -1,0 +1,491 @@
+#!/usr/bin/env python
+"""bench.py -- the headline benchmark of BASELINE.json: rasterizer forward+backward at 1080p on the 3M-Gaussian,
+SH-degree-3 scene (config C3), reported as views/s over all GPUs and ms per view.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+
+A STEP is one batch of `--views-per-step` (default 8) distinct cameras per GPU: forward + backward of every view
+through the public operator API (GaussianRasterizer + autograd), per-Gaussian gradients accumulated on the device,
+and -- for N > 1 -- one NCCL sum all-reduce of the 59-float/Gaussian gradient bucket (view-parallel data parallelism,
+weak scaling: per-GPU work is fixed). Inputs (708 MB of Gaussian parameters per replica) exceed the 126 MB L2, so no
+explicit flush is needed between iterations.
+
+One JSON line is printed by rank 0. Keys beyond the base contract:
+  roofline      dominant kernel of the step (by device time, CUDA events on the launching stream inside the timed
+                region) against the ceiling that bounds it; roofline_hbm: the same for the most expensive HBM-bound
+                kernel against the measured copy bandwidth of MEASURED_PEAKS.json; kernels: the full per-kernel table.
+  cpu_baseline  the C restatement of the reference algorithm (oracle/, OpenMP) timed on the host cores on a bounded
+                sample of the same workload (rank 0, N=1 only). Checker code: measured here, never shipped.
+  e2e           the same metric through the same API with HOST buffers: every view's camera and dL/dpixel come from
+                pinned host memory and the rendered image goes back to pinned host memory inside the timed region.
+`--impl reference` times the UNMODIFIED reference CUDA rasterizer (oracle/_ref/ref_dgr_C.so, built from
+/root/reference by oracle/Makefile) on the same step; if that build is absent it times the CPU restatement instead.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "gaussian-splatting-slam_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "rasterizer fwd+bwd views/s @1080p, 3M Gaussians SH3 (ms/iter = 1000 * n_gpus / value)"
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # no SIMT figure in MEASURED_PEAKS.json: 148 SM x 128 FMA/clk x max clock
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--views-per-step", type=int, default=8)
+    ap.add_argument("--gaussians", type=int, default=3_000_000)
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-kernel-timing", action="store_true")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------- workload
+def build_workload(args, rank, world, dev):
+    import torch
+    import scenes
+    sc = scenes.make_c3(P=args.gaussians)
+    n_views = args.views_per_step * world
+    cams = scenes.c3_cameras(n=n_views, W=args.width, H=args.height, jitter=0.05 if n_views > 8 else 0.0)
+    from view_parallel import shard_views
+    mine = [cams[i] for i in shard_views(n_views, rank, world)]
+    g = torch.Generator().manual_seed(1000 + rank)
+    dpix_host = torch.randn(3, args.height, args.width, generator=g).pin_memory() if dev.type == "cuda" else \
+        torch.randn(3, args.height, args.width, generator=g)
+    return sc, mine, dpix_host
+
+
+def device_params(sc, dev):
+    import torch
+    names = ("means3D", "shs", "opacities", "scales", "rotations")
+    return {n: getattr(sc, n).to(dev).contiguous().requires_grad_(True) for n in names}
+
+
+class OursArm:
+    name = "ours"
+
+    def __init__(self, args, sc, cams, dpix_host, dev):
+        import torch
+        from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, _C
+        from view_parallel import GradBucket
+        self.torch, self._C = torch, _C
+        self.Settings, self.Rasterizer = GaussianRasterizationSettings, GaussianRasterizer
+        self.dev, self.args, self.deg = dev, args, sc.sh_degree
+        self.params = device_params(sc, dev)
+        self.means2D = torch.zeros_like(self.params["means3D"], requires_grad=True)    # the caller's grad sink
+        self.bucket = GradBucket(self.params)
+        self.bg = torch.zeros(3, device=dev)
+        self.cams_host = cams
+        self.cams_dev = [(c.viewmatrix.to(dev), c.projmatrix.to(dev), c.campos.to(dev)) for c in cams]
+        self.dpix_host = dpix_host
+        self.dpix = dpix_host.to(dev)
+        # pinned staging for the end-to-end leg
+        self.cam_pinned = [torch.cat([c.viewmatrix.reshape(-1), c.projmatrix.reshape(-1), c.campos.reshape(-1)]).pin_memory()
+                           for c in cams]
+        self.cam_dev_buf = torch.empty(35, device=dev)
+        self.dpix_dev_buf = torch.empty_like(self.dpix)
+        self.color_host = torch.empty(3, args.height, args.width).pin_memory()
+        self.last = None
+
+    def _settings(self, cam, view, proj, campos):
+        return self.Settings(image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=self.bg,
+                             scale_modifier=1.0, viewmatrix=view, projmatrix=proj, sh_degree=self.deg, campos=campos,
+                             prefiltered=False, debug=False, antialiasing=False)
+
+    def _view(self, st, dpix):
+        p = self.params
+        color, radii, _invd = self.Rasterizer(st)(means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"],
+                                                  shs=p["shs"], scales=p["scales"], rotations=p["rotations"])
+        self.torch.autograd.backward([color], [dpix])
+        self.last = (color, radii)
+        return color
+
+    def step(self):
+        self.bucket.zero()
+        self.bucket.attach()
+        self.means2D.grad = None
+        for cam, (v, pj, cp) in zip(self.cams_host, self.cams_dev):
+            self._view(self._settings(cam, v, pj, cp), self.dpix)
+        self.bucket.all_reduce()
+
+    def step_e2e(self):
+        """Same step, host buffers: camera + dL/dpixel H2D from pinned memory, rendered image D2H, every view."""
+        self.bucket.zero()
+        self.bucket.attach()
+        self.means2D.grad = None
+        for cam, pinned in zip(self.cams_host, self.cam_pinned):
+            self.cam_dev_buf.copy_(pinned, non_blocking=True)
+            self.dpix_dev_buf.copy_(self.dpix_host, non_blocking=True)
+            b = self.cam_dev_buf
+            color = self._view(self._settings(cam, b[0:16].view(4, 4), b[16:32].view(4, 4), b[32:35]), self.dpix_dev_buf)
+            self.color_host.copy_(color.detach(), non_blocking=True)
+        self.bucket.all_reduce()
+
+    def state_of_view(self, i):
+        """Forward of view i through the binding (outside any timed region) and its decoded scratch state."""
+        cam, (v, pj, cp) = self.cams_host[i], self.cams_dev[i]
+        p = {k: t.detach() for k, t in self.params.items()}
+        e = self.torch.empty(0, device=self.dev)
+        R, _color, radii, geom, binning, img, _ = self._C.rasterize_gaussians(
+            self.bg, p["means3D"], e, p["opacities"], p["scales"], p["rotations"], 1.0, e, v, pj, cam.tanfovx, cam.tanfovy,
+            cam.H, cam.W, p["shs"], self.deg, cp, False, False, False)
+        return R, radii, self._C.decode_state(self.args.gaussians, R, cam.W, cam.H, geom, binning, img)
+
+    def e2e_bytes(self):
+        n = len(self.cams_host)
+        return n * (35 * 4 + self.dpix_host.numel() * 4), n * self.color_host.numel() * 4
+
+    def launches(self):
+        return self._C.launch_count()
+
+
+class ReferenceArm:
+    """The unmodified reference CUDA rasterizer behind the same step (autograd wrapper = harness, oracle/ref_cuda.py)."""
+    name = "reference"
+
+    def __init__(self, args, sc, cams, dpix_host, dev):
+        import torch
+        from oracle import ref_cuda
+        from view_parallel import GradBucket
+        self.torch, self.ref = torch, ref_cuda
+        self.dev, self.deg = dev, sc.sh_degree
+        self.params = device_params(sc, dev)
+        self.means2D = torch.zeros_like(self.params["means3D"], requires_grad=True)
+        self.bucket = GradBucket(self.params)
+        self.bg = torch.zeros(3, device=dev)
+        self.cams_host = cams
+        self.cams_dev = [(c.viewmatrix.to(dev), c.projmatrix.to(dev), c.campos.to(dev)) for c in cams]
+        self.dpix = dpix_host.to(dev)
+        self.fn = ref_cuda.autograd_function()
+
+    def step(self):
+        self.bucket.zero()
+        self.bucket.attach()
+        self.means2D.grad = None
+        p = self.params
+        for cam, (v, pj, cp) in zip(self.cams_host, self.cams_dev):
+            color, _radii = self.fn.apply(p["means3D"], self.means2D, p["shs"], p["opacities"], p["scales"], p["rotations"],
+                                          dict(bg=self.bg, viewmatrix=v, projmatrix=pj, campos=cp, tanfovx=cam.tanfovx,
+                                               tanfovy=cam.tanfovy, H=cam.H, W=cam.W, sh_degree=self.deg))
+            self.torch.autograd.backward([color], [self.dpix])
+
+    def launches(self):
+        return 0
+
+
+# ----------------------------------------------------------------------------------------------- work model
+def work_model(arm, args):
+    """Algorithmic work per VIEW for every kernel name (SURVEY.md 8d / DESIGN.md 'Roofline accounting'), taken from the
+    state of the last rendered view. HBM kernels: bytes; blend kernels: FP32 flop."""
+    import torch
+    P = args.gaussians
+    R, radii, st = arm.state_of_view(len(arm.cams_host) - 1)
+    visible = int((radii > 0).sum())
+    traversed = int(st["n_contrib"].to(torch.int64).sum())
+    tiles = ((args.width + 15) // 16) * ((args.height + 15) // 16)
+    N = args.width * args.height
+    sort_tiles_P, sort_tiles_R = (P + 4095) // 4096, (R + 4095) // 4096
+    tb = max(1, math.ceil(math.log2(tiles)))
+    rp = (tb + 7) // 8
+    w = {
+        # per visible Gaussian 311 B (read 236 + write 75), per culled one 20 B
+        "preprocess_fwd": ("hbm", 311.0 * visible + 20.0 * (P - visible)),
+        # (P-sort: 4 passes) + (R-sort: rp passes): hist reads 4 B/key, scatter reads 8 + writes 8 B/pair
+        "digit_hist": ("hbm", 4.0 * (4 * P + rp * R)),
+        "digit_scan": ("hbm", 8.0 * 256 * (4 * sort_tiles_P + rp * sort_tiles_R)),
+        "digit_scatter": ("hbm", 16.0 * (4 * P + rp * R)),
+        "scan_reduce": ("hbm", 8.0 * P), "scan_spine": ("hbm", 8.0 * ((P + 2047) // 2048)),
+        "scan_apply": ("hbm", 12.0 * P),
+        "emit_instances": ("hbm", 8.0 * P + 28.0 * visible + 8.0 * R),
+        "tile_ranges": ("hbm", 4.0 * R + 8.0 * tiles),
+        # 13 flop for every (pixel, list entry) pair up to the pixel's last contributor (power + alpha test); the 9
+        # further flop of a contributing pair are not counted (lower bound)
+        "blend_forward": ("fp32", 13.0 * traversed),
+        "blend_backward": ("fp32", 13.0 * traversed),
+        "memset_grad_acc": ("hbm", 48.0 * P),
+        "preprocess_bwd": ("hbm", 563.0 * visible + (4.0 + 236.0) * (P - visible)),
+    }
+    return w, dict(num_rendered=R, visible=visible, traversed_pairs=traversed, mean_list_len=R / tiles, pixels=N)
+
+
+def kernel_table(report, views):
+    rows = {}
+    for line in report.strip().splitlines():
+        name, n, ms = line.split()
+        rows[name] = {"launches_per_view": int(n) / views, "ms_per_view": float(ms) / views}
+    return rows
+
+
+def roofline_entry(name, row, work, peaks, traffic=None):
+    bound, amount = work[name]
+    per_launch = amount / max(row["launches_per_view"], 1e-9)
+    dur_s = row["ms_per_view"] / max(row["launches_per_view"], 1e-9) / 1e3
+    if bound == "hbm":
+        achieved, unit = per_launch / dur_s / 1e9, "GB/s"
+        peak = peaks.get("hbm_gbs") or 6650.0
+        src = "measured copy bandwidth (MEASURED_PEAKS.json)" if peaks.get("hbm_gbs") else "fallback 6.65 TB/s"
+    else:
+        achieved, unit = per_launch / dur_s / 1e12, "TFLOP/s"
+        peak, src = FP32_PEAK_TFLOPS, "computed FP32 SIMT peak 148 SM x 128 FMA/clk x 1.965 GHz (MEASURED_PEAKS.json has no SIMT figure)"
+    return {"kernel": name, "bound": bound, "achieved": round(achieved, 3), "peak": round(peak, 1), "unit": unit,
+            "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": src,
+            "avg_launch_ms": round(dur_s * 1e3, 4), "share_of_step": None}
+
+
+# ----------------------------------------------------------------------------------------------- cpu baseline
+def cpu_baseline(args):
+    """C restatement (oracle/gsr_oracle.c, OpenMP) on the host cores: full forward + backward of ONE view of the same
+    scene and camera set (a bounded sample of the 8-view step)."""
+    import numpy as np
+    import scenes
+    from oracle import c_oracle
+    c_oracle.build()
+    cores = os.cpu_count() or 1
+    c_oracle.set_threads(cores)
+    sc = scenes.make_c3(P=args.gaussians)
+    cam = scenes.c3_cameras(n=8, W=args.width, H=args.height)[0]
+    S = c_oracle.Scene(W=cam.W, H=cam.H, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=np.zeros(3, np.float32),
+                       means3D=sc.means3D.numpy(), opacities=sc.opacities.numpy(), viewmatrix=cam.viewmatrix.numpy(),
+                       projmatrix=cam.projmatrix.numpy(), campos=cam.campos.numpy(), sh_degree=sc.sh_degree,
+                       shs=sc.shs.numpy(), scales=sc.scales.numpy(), rotations=sc.rotations.numpy())
+    dpix = np.random.default_rng(0).standard_normal((3, cam.H, cam.W)).astype(np.float32)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        fw = c_oracle.forward(S, want_invdepth=False)
+        c_oracle.backward(S, fw, dpix, None)
+        n += 1
+        el = time.perf_counter() - t0
+        if el > 10.0 or n >= 4:
+            break
+    return {"value": round(n / el, 4), "unit": "views/s", "cores": c_oracle.num_threads(), "kind": "port",
+            "sample": f"{n} full fwd+bwd view(s) of the same {args.gaussians}-Gaussian scene at {args.width}x{args.height} "
+                      f"(camera 0 of the step) by oracle/gsr_oracle.c with OpenMP, {el:.1f} s"}
+
+
+# ----------------------------------------------------------------------------------------------- main
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference" and rank != 0:
+        return 0
+    import torch
+    if not torch.cuda.is_available():
+        if args.impl == "reference":
+            cb = cpu_baseline(args)
+            print(json.dumps({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "views/s", "n_gpus": 0,
+                              "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "cpu_baseline": cb,
+                              "e2e": {"value": cb["value"], "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+            return 0
+        raise SystemExit("bench.py needs a CUDA device: the rasterizer has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    import torch.distributed as dist
+    ref_world = 1 if args.impl == "reference" else world
+    if ref_world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    sc, cams, dpix_host = build_workload(args, rank if ref_world > 1 else 0, ref_world, dev)
+    if args.impl == "reference":
+        from oracle import ref_cuda
+        if not ref_cuda.available():
+            cb = cpu_baseline(args)
+            print(json.dumps({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "views/s", "n_gpus": 1,
+                              "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "cpu_baseline": cb,
+                              "ms_per_step": None, "config": {"workload": "C3 (CPU port: reference CUDA build absent)"},
+                              "e2e": {"value": cb["value"], "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+            return 0
+        arm = ReferenceArm(args, sc, cams, dpix_host, dev)
+    else:
+        arm = OursArm(args, sc, cams, dpix_host, dev)
+
+    def barrier():
+        if ref_world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, prof=False):
+        """K steps bracketed by barrier + synchronize on both sides; device time by CUDA events, max over ranks."""
+        barrier()
+        if prof:
+            arm._C.profile_enable(True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        if prof:
+            arm._C.profile_enable(False)
+        ms = torch.tensor([e0.elapsed_time(e1), wall], device=dev, dtype=torch.float64)
+        if ref_world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms[0]), float(ms[1])
+
+    for _ in range(max(args.warmup, 0)):
+        arm.step()
+    barrier()
+
+    prof = args.impl == "ours" and not args.no_kernel_timing
+    l0 = arm.launches()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_total, _wall = timed(arm.step, args.steps, prof=prof)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = arm.launches() - l0
+    views = args.views_per_step * args.steps
+    ms_per_step = ms_total / args.steps
+    value = ref_world * views / (ms_total / 1e3)
+
+    kernels, roof, roof_hbm, stats = None, None, None, None
+    if prof:
+        report = arm._C.profile_report()
+        if report:
+            kernels = kernel_table(report, views)
+            work, stats = work_model(arm, args)
+            peaks = {}
+            try:
+                peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            except Exception:
+                pass
+            ms_view = ms_per_step / args.views_per_step
+            traffic = {}
+            try:
+                traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            except Exception:
+                pass
+            known = [k for k in kernels if k in work]
+            top = max(known, key=lambda k: kernels[k]["ms_per_view"])
+            roof = roofline_entry(top, kernels[top], work, peaks, traffic.get(top))
+            roof["share_of_step"] = round(kernels[top]["ms_per_view"] / ms_view, 4)
+            hbm = [k for k in known if work[k][0] == "hbm"]
+            if hbm:
+                th = max(hbm, key=lambda k: kernels[k]["ms_per_view"])
+                roof_hbm = roofline_entry(th, kernels[th], work, peaks, traffic.get(th))
+                roof_hbm["share_of_step"] = round(kernels[th]["ms_per_view"] / ms_view, 4)
+            for k in kernels:
+                kernels[k] = {a: round(b, 4) for a, b in kernels[k].items()}
+                if k in work:
+                    kernels[k]["frac_of_roofline"] = roofline_entry(k, kernels[k], work, peaks)["frac"] \
+                        if kernels[k]["ms_per_view"] > 0 else None
+
+    e2e = None
+    if args.impl == "ours" and not args.no_e2e:
+        arm.step_e2e()
+        _dev_ms, wall_ms = timed(arm.step_e2e, args.steps)
+        h2d, d2h = arm.e2e_bytes()
+        e2e = {"value": round(ref_world * views / (wall_ms / 1e3), 3), "unit": "views/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "timing": "host wall clock around K steps incl. pinned H2D/D2H, max over ranks"}
+
+    cb = None
+    if rank == 0 and world == 1 and args.impl == "ours" and not args.no_cpu_baseline:
+        del arm
+        torch.cuda.empty_cache()
+        cb = cpu_baseline(args)
+
+    if rank == 0:
+        out = {"metric": METRIC, "value": round(value, 3), "unit": "views/s", "n_gpus": ref_world, "steps": args.steps,
+               "warmup": args.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+               "fwd_bwd_ms_per_iter": round(ms_per_step / args.views_per_step, 4),
+               "config": {"workload": f"C3: {args.gaussians} Gaussians SH3 (Mip-NeRF360-scale mixture, seed 2), "
+                                      f"{args.width}x{args.height}, orbit cameras; rasterizer forward+backward",
+                          "views_per_step_per_gpu": args.views_per_step, "global_views_per_step": args.views_per_step * ref_world,
+                          "parallelism": f"view-parallel dp{ref_world}, replicated Gaussians" +
+                                         (", NCCL all-reduce of 59 floats/Gaussian per step" if ref_world > 1 else ""),
+                          "l2": "inputs (708 MB parameters + 300 MB scratch per view) exceed the 126 MB L2; no explicit flush"},
+               "clocks": clocks, "gpu_launches": launches}
+        if args.impl == "reference":
+            out["impl"] = "reference"
+            out["cpu_baseline"] = {"value": out["value"], "unit": "views/s", "cores": 0, "kind": "reference",
+                                   "sample": "the reference has no CPU rasterizer: this arm is its own unmodified CUDA "
+                                             "rasterizer (oracle/_ref/ref_dgr_C.so) on one B200, same step"}
+            out["e2e"] = {"value": out["value"], "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+            out["gpu_launches"] = None
+        else:
+            out["e2e"] = e2e
+            out["roofline"] = roof
+            out["roofline_hbm"] = roof_hbm
+            out["cpu_baseline"] = cb
+            out["workload_stats"] = stats
+            out["kernels"] = kernels
+        print(json.dumps(out))
+    if ref_world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -3,10 +3,35 @@
 #include "gsr_common.cuh"
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
+#include <map>
+#include <string>
+#include <vector>
 
 namespace gsr {
 
 unsigned long long g_launches = 0;
+
+// ---- optional per-launch timing (bench.py's roofline leg): one CUDA-event pair per launch on the launching
+// stream, resolved at report time. Off by default; costs nothing when off.
+bool g_prof_on = false;
+namespace {
+struct ProfRec { const char* name; cudaEvent_t a, b; };
+std::vector<ProfRec> g_prof_recs;
+std::vector<cudaEvent_t> g_prof_pool;
+cudaEvent_t prof_event() {
+    cudaEvent_t e;
+    if (!g_prof_pool.empty()) { e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+    cudaEventCreate(&e);
+    return e;
+}
+}  // namespace
+void prof_begin(const char* what, cudaStream_t s) {
+    ProfRec r{what, prof_event(), prof_event()};
+    cudaEventRecord(r.a, s);
+    g_prof_recs.push_back(r);
+}
+void prof_end(cudaStream_t s) { cudaEventRecord(g_prof_recs.back().b, s); }
 
 int check_launch(const char* what, bool debug, cudaStream_t s) {
     cudaError_t e = cudaGetLastError();
@@ -61,6 +86,48 @@ int gsr_key_bits(int W, int H) { return 32 + (int)higher_msb((uint32_t)tiles_of(
 size_t gsr_backward_scratch_bytes(int P) { return sizeof(float) * GSR_ACC_FLOATS * (size_t)(P > 0 ? P : 0) + 256; }
 size_t gsr_dist2_temp_bytes(int P) { return dist2_temp_bytes(P); }
 uint64_t gsr_launch_count(void) { return g_launches; }
+
+int gsr_profile_enable(int on) {
+    if (on) {   // a new recording starts: recycle the previous log's events
+        for (auto& r : g_prof_recs) { g_prof_pool.push_back(r.a); g_prof_pool.push_back(r.b); }
+        g_prof_recs.clear();
+    }
+    g_prof_on = on != 0;
+    return 0;
+}
+
+long gsr_profile_report(char* buf, size_t cap) {
+    struct Agg { long n = 0; double ms = 0.0; int first = 0; };
+    std::map<std::string, Agg> agg;
+    int order = 0;
+    for (auto& r : g_prof_recs) {
+        cudaError_t e = cudaEventSynchronize(r.b);
+        if (e != cudaSuccess) return -(long)e;
+        float ms = 0.f;
+        e = cudaEventElapsedTime(&ms, r.a, r.b);
+        if (e != cudaSuccess) return -(long)e;
+        Agg& a = agg[r.name];
+        if (a.n == 0) a.first = order++;
+        a.n++;
+        a.ms += ms;
+    }
+    std::vector<std::pair<int, std::string>> names;
+    for (auto& kv : agg) names.push_back({kv.second.first, kv.first});
+    std::sort(names.begin(), names.end());
+    std::string out;
+    char line[256];
+    for (auto& nm : names) {
+        const Agg& a = agg[nm.second];
+        snprintf(line, sizeof(line), "%s %ld %.6f\n", nm.second.c_str(), a.n, a.ms);
+        out += line;
+    }
+    if (buf && cap > 0) {
+        const size_t n = out.size() < cap - 1 ? out.size() : cap - 1;
+        memcpy(buf, out.data(), n);
+        buf[n] = 0;
+    }
+    return (long)out.size() + 1;
+}
 const char* gsr_version(void) { return "gsr 0.1 (sm_100a)"; }
 
 const char* gsr_error_string(int code) {
@@ -162,8 +229,7 @@ int gsr_backward(const gsr_view* view, int R, const int* radii, const char* geom
     }
     char* ap = accum_scratch;
     float* acc = carve<float>(ap, (size_t)v.P * GSR_ACC_FLOATS);
-    cudaError_t ce = cudaMemsetAsync(acc, 0, sizeof(float) * GSR_ACC_FLOATS * (size_t)v.P, s);
-    if (ce != cudaSuccess) return (int)ce;
+    GSR_MEMSET("memset_grad_acc", s, acc, 0, sizeof(float) * GSR_ACC_FLOATS * (size_t)v.P);
     int e = 0;
     if (R > 0) {
         e = launch_blend_backward(v, g, b, img, dL_dpix, dL_dinvdepth, acc, s);

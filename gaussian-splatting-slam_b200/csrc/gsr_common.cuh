@@ -12,13 +12,26 @@ namespace gsr {
 
 // ---------------------------------------------------------------- launch accounting / checks
 extern unsigned long long g_launches;
+extern bool g_prof_on;                               // gsr_profile_enable(): CUDA-event pair around every launch
 int check_launch(const char* what, bool debug, cudaStream_t s);
+void prof_begin(const char* what, cudaStream_t s);
+void prof_end(cudaStream_t s);
 #define GSR_LAUNCH(what, debug, stream, ...)                 \
     do {                                                     \
+        if (gsr::g_prof_on) gsr::prof_begin(what, stream);   \
         __VA_ARGS__;                                         \
+        if (gsr::g_prof_on) gsr::prof_end(stream);           \
         gsr::g_launches++;                                   \
         int _e = gsr::check_launch(what, debug, stream);     \
         if (_e) return _e;                                   \
+    } while (0)
+// memsets: timed like launches when profiling, not counted as kernels
+#define GSR_MEMSET(what, stream, ptr, val, bytes)                                  \
+    do {                                                                           \
+        if (gsr::g_prof_on) gsr::prof_begin(what, stream);                         \
+        cudaError_t _ce = cudaMemsetAsync(ptr, val, bytes, stream);                \
+        if (gsr::g_prof_on) gsr::prof_end(stream);                                 \
+        if (_ce != cudaSuccess) return (int)_ce;                                   \
     } while (0)
 
 // ---------------------------------------------------------------- scratch layouts (private)

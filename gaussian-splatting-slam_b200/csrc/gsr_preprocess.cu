@@ -76,9 +76,17 @@ __device__ __forceinline__ void cov3d_of(const V3 scale, float mod, const float4
     M3 S = make_m3(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
     S.c[0][0] = mod * scale.x; S.c[1][1] = mod * scale.y; S.c[2][2] = mod * scale.z;
     float r = q.x, x = q.y, y = q.z, z = q.w;
-    M3 R = make_m3(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-                   2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-                   2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    // The nine entries share products, and which product of "a*b +- c*d" ends up inside the FMA decides the
+    // last bit. Pinned with explicit intrinsics to the choice ptxas makes for the reference (its SASS).
+    const float xz = __fmul_rn(x, z), rx = __fmul_rn(r, x), rz = __fmul_rn(r, z);
+    const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+    const float xz_p_ry = __fmaf_rn(r, y, xz), xz_m_ry = __fmaf_rn(-r, y, xz);
+    const float yz_m_rx = __fmaf_rn(y, z, -rx), yz_p_rx = __fmaf_rn(y, z, rx);
+    const float xy_m_rz = __fmaf_rn(x, y, -rz), xy_p_rz = __fmaf_rn(x, y, rz);
+    const float xx_p_yy = __fmaf_rn(x, x, yy), yy_p_zz = __fadd_rn(yy, zz), xx_p_zz = __fmaf_rn(x, x, zz);
+    M3 R = make_m3(__fsub_rn(1.f, __fadd_rn(yy_p_zz, yy_p_zz)), __fadd_rn(xy_m_rz, xy_m_rz), __fadd_rn(xz_p_ry, xz_p_ry),
+                   __fadd_rn(xy_p_rz, xy_p_rz), __fsub_rn(1.f, __fadd_rn(xx_p_zz, xx_p_zz)), __fadd_rn(yz_m_rx, yz_m_rx),
+                   __fadd_rn(xz_m_ry, xz_m_ry), __fadd_rn(yz_p_rx, yz_p_rx), __fsub_rn(1.f, __fadd_rn(xx_p_yy, xx_p_yy)));
     M3 Mm = mul(S, R);
     M3 Sigma = mul(transpose(Mm), Mm);
     cov3D[0] = Sigma.c[0][0]; cov3D[1] = Sigma.c[0][1]; cov3D[2] = Sigma.c[0][2];

@@ -54,6 +54,10 @@ def lib():
             getattr(L, n).restype = C.c_size_t
         L.gsr_required_binning.restype = C.c_size_t
         L.gsr_launch_count.restype = C.c_uint64
+        L.gsr_profile_enable.restype = C.c_int
+        L.gsr_profile_enable.argtypes = [C.c_int]
+        L.gsr_profile_report.restype = C.c_long
+        L.gsr_profile_report.argtypes = [C.c_char_p, C.c_size_t]
         L.gsr_error_string.restype = C.c_char_p
         L.gsr_version.restype = C.c_char_p
         for n in ("gsr_geom_layout", "gsr_image_layout"):
@@ -214,6 +218,20 @@ def mark_visible(means3D, viewmatrix, projmatrix):
 
 def launch_count():
     return int(lib().gsr_launch_count())
+
+
+def profile_enable(on):
+    """Per-launch CUDA-event timing inside libgsr.so (bench.py's roofline leg); enabling clears the log."""
+    _check(lib().gsr_profile_enable(1 if on else 0), "gsr_profile_enable")
+
+
+def profile_report():
+    """'<kernel> <launches> <total_ms>' lines for everything launched since profile_enable(True)."""
+    buf = C.create_string_buffer(1 << 16)
+    n = lib().gsr_profile_report(buf, len(buf))
+    if n < 0:
+        _check(int(-n), "gsr_profile_report")
+    return buf.value.decode()
 
 
 def decode_state(P, R, W, H, geomBuffer, binningBuffer, imgBuffer, view_args=None):

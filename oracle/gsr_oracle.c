@@ -64,14 +64,20 @@ void gso_set_threads(int n) {
 }
 
 /* auxiliary.h:58-77 : matrices are read column-major (= transposed torch matrices). */
+/* The reference is built with nvcc's default -fmad=true; for these four-term sums its SASS is
+   mul(second term), fma(first), fma(third), add(fourth). Written out with fmaf() so that view-space
+   depth (the low half of the sort keys) and the projected means carry the reference's exact bits. */
+static inline float xf_row(float a, float b, float c, float d, const float *p) {
+    return fmaf(c, p[2], fmaf(a, p[0], b * p[1])) + d;
+}
 static inline void xf43(const float *p, const float *m, float *o) {
-    o[0] = m[0] * p[0] + m[4] * p[1] + m[8] * p[2] + m[12];
-    o[1] = m[1] * p[0] + m[5] * p[1] + m[9] * p[2] + m[13];
-    o[2] = m[2] * p[0] + m[6] * p[1] + m[10] * p[2] + m[14];
+    o[0] = xf_row(m[0], m[4], m[8], m[12], p);
+    o[1] = xf_row(m[1], m[5], m[9], m[13], p);
+    o[2] = xf_row(m[2], m[6], m[10], m[14], p);
 }
 static inline void xf44(const float *p, const float *m, float *o) {
     xf43(p, m, o);
-    o[3] = m[3] * p[0] + m[7] * p[1] + m[11] * p[2] + m[15];
+    o[3] = xf_row(m[3], m[7], m[11], m[15], p);
 }
 
 /* auxiliary.h:41-44 : evaluated in double because of the 1.0 / 0.5 literals. */

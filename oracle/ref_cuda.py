@@ -113,3 +113,23 @@ def mark_visible(means3D, viewmatrix, projmatrix):
 
 def dist2(points):
     return knn().distCUDA2(points)
+
+
+def autograd_function():
+    """torch.autograd.Function around the reference's two pybind entry points, for bench.py's `--impl reference`
+    arm (harness code: same call order as the reference's own Python wrapper, written for keyword settings)."""
+    class _RefRasterize(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, means3D, means2D, shs, opacities, scales, rotations, st):
+            fw = forward(means3D=means3D, shs=shs, opacities=opacities, scales=scales, rotations=rotations, **st)
+            ctx.fw = fw
+            ctx.mark_non_differentiable(fw["radii"])
+            return fw["color"], fw["radii"]
+
+        @staticmethod
+        def backward(ctx, dL_dcolor, _):
+            g = backward(ctx.fw, dL_dcolor.contiguous())
+            ctx.fw = None
+            return (g["dL_dmeans3D"], g["dL_dmeans2D"], g["dL_dsh"], g["dL_dopacity"], g["dL_dscales"],
+                    g["dL_drotations"], None)
+    return _RefRasterize

@@ -1,0 +1,90 @@
+"""CPU tests (-m "not gpu") of the multi-GPU host logic with the gloo backend, world_size 2:
+view sharding, the flat gradient bucket, the single exchange step, and 1-vs-2-rank gradient equality."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from view_parallel import GradBucket, reduce_densification_stats, shard_views
+
+
+def test_shard_views_partitions_every_batch():
+    for n in (0, 1, 7, 8, 64):
+        for world in (1, 2, 3, 8):
+            parts = [shard_views(n, r, world) for r in range(world)]
+            assert sorted(sum(parts, [])) == list(range(n))
+            assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
+    assert shard_views(8, 1, 4) == [1, 5]
+    with pytest.raises(ValueError):
+        shard_views(8, 4, 4)
+
+
+def test_grad_bucket_views_alias_flat_storage_and_autograd_accumulates_in_place():
+    p = {"a": torch.randn(5, 3, requires_grad=True), "b": torch.randn(7, requires_grad=True)}
+    bk = GradBucket(p)
+    assert bk.flat.numel() % 32 == 0 and all(o % 32 == 0 for o in bk.offsets.values())
+    bk.attach()
+    for _ in range(3):
+        ((p["a"] * 2).sum() + (p["b"] * 3).sum()).backward()
+    assert p["a"].grad.data_ptr() == bk.views["a"].data_ptr()
+    assert torch.allclose(bk.views["a"], torch.full((5, 3), 6.0)) and torch.allclose(bk.views["b"], torch.full((7,), 9.0))
+    bk.zero()
+    assert float(bk.flat.abs().sum()) == 0.0 and float(p["a"].grad.abs().sum()) == 0.0
+    assert bk.all_reduce() is None          # no process group: a no-op
+    with pytest.raises(ValueError):
+        GradBucket({})
+    with pytest.raises(ValueError):
+        GradBucket({"h": torch.zeros(3, dtype=torch.float16)})
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _toy_view_loss(params, view):
+    # a differentiable stand-in for "render view v": each view weights the parameters differently
+    w = torch.linspace(0.5, 1.5, params["x"].numel()).view_as(params["x"]) * (view + 1)
+    return (params["x"] * w).sin().sum() + (params["y"] ** 2).sum() * (view + 1)
+
+
+def _worker(rank, world, port, n_views, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = torch.Generator().manual_seed(0)                       # replicated parameters
+        params = {"x": torch.randn(6, 3, generator=g).requires_grad_(True),
+                  "y": torch.randn(11, generator=g).requires_grad_(True)}
+        bk = GradBucket(params)
+        bk.zero(); bk.attach()
+        for v in shard_views(n_views, rank, world):
+            _toy_view_loss(params, v).backward()
+        bk.all_reduce()
+        acc, den, mx = torch.full((4,), float(rank + 1)), torch.ones(4), torch.tensor([1.0, 5.0, 2.0, 0.0]) * (rank + 1)
+        reduce_densification_stats(acc, den, mx)
+        if rank == 0:
+            torch.save({"flat": bk.flat.clone(), "acc": acc, "den": den, "mx": mx}, out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_views", [8, 5])
+def test_two_ranks_equal_one_rank(tmp_path, n_views):
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_worker, args=(2, _free_port(), n_views, out), nprocs=2, join=True)
+    got = torch.load(out)
+    g = torch.Generator().manual_seed(0)
+    params = {"x": torch.randn(6, 3, generator=g).requires_grad_(True), "y": torch.randn(11, generator=g).requires_grad_(True)}
+    bk = GradBucket(params)
+    bk.attach()
+    for v in range(n_views):
+        _toy_view_loss(params, v).backward()
+    assert torch.allclose(got["flat"], bk.flat, rtol=1e-5, atol=1e-6)
+    assert torch.equal(got["acc"], torch.full((4,), 3.0)) and torch.equal(got["den"], torch.full((4,), 2.0))
+    assert torch.equal(got["mx"], torch.tensor([2.0, 10.0, 4.0, 0.0]))

