@@ -100,7 +100,7 @@ def _check_forward_vs_oracle(ours, fw, tag, int_slack=2e-4):
     return exact
 
 
-def _check_grads(g_ours, g_ref, tag, names):
+def _check_grads(g_ours, g_ref, tag, names, tol=None):
     for ours_name, ref_name in names:
         if ref_name not in g_ref or g_ref[ref_name] is None or ours_name not in g_ours:
             continue
@@ -109,7 +109,8 @@ def _check_grads(g_ours, g_ref, tag, names):
             assert np.linalg.norm(a) == 0, f"{tag} {ours_name}: expected zero gradient"
             continue
         e = rel_l2(a.reshape(b.shape), b)
-        assert e <= GRAD_TOL, f"{tag} grad {ours_name}: rel-L2 {e:.3e}"
+        t = GRAD_TOL if tol is None else max(GRAD_TOL, tol.get(ref_name, 0.0))
+        assert e <= t, f"{tag} grad {ours_name}: rel-L2 {e:.3e} (tolerance {t:.3e})"
 
 
 ORACLE_GRADS = [("means3D", "dL_dmean3D"), ("means2D", "dL_dmean2D"), ("opacities", "dL_dopacity"), ("shs", "dL_dsh"),
@@ -191,12 +192,19 @@ def _case(sc, cam, bg, seed=0, aa=False, depth_grad=False, vs_ref=True, f64_arbi
     d = np.abs(ours["invdepth"] - fw["invdepth"])
     assert float((d > IMG_TOL).mean()) <= 2e-4, f"invdepth max {d.max():.3e}"
     g = c_oracle.backward(S, fw, dpix, dinv)
+    tol = None
     if f64_arbiter:
+        # Truth = float64 autograd. Bar per tensor: 1e-4, or -- for the ill-conditioned ones (the rotation gradient is
+        # the antisymmetric part of an almost symmetric matrix) -- 1.25x the error a plain fp32 evaluation (the C
+        # restatement) itself has against the truth: the kernel must be as accurate as fp32 allows.
         g64 = _f64_autograd_grads(sc, cam, bg, aa, dpix, dinv)
+        tol = {}
         for k, v in g64.items():
-            assert rel_l2(g[k].reshape(v.shape), v) <= 2e-4, f"C oracle vs float64 autograd, {k}"
+            e32 = rel_l2(g[k].reshape(v.shape), v)
+            assert e32 <= 3e-4, f"C oracle vs float64 autograd, {k}: {e32:.3e}"
+            tol[k] = 1.25 * e32
             g[k] = v.astype(np.float32).reshape(g[k].shape)
-    _check_grads(ours["grads"], g, "oracle", ORACLE_GRADS)
+    _check_grads(ours["grads"], g, "oracle", ORACLE_GRADS, tol)
     if vs_ref and not aa and not depth_grad:
         _check_vs_reference_cuda(ours, sc, cam, bg, dpix, "C", **kw)
     return ours, fw
