@@ -514,28 +514,36 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
         }
     }
 
-    // ---- write everything (zeros for invisible Gaussians)
-    o.dL_dmeans2D[3 * (size_t)idx + 0] = dmean2d[0];
+    // ---- write everything (zeros for invisible Gaussians); in accumulate mode add to what is there and leave the
+    // rows of invisible Gaussians untouched (multi-view batches: no zero fill, no separate accumulation pass)
+    const bool accum = o.accumulate != 0;
+    o.dL_dmeans2D[3 * (size_t)idx + 0] = dmean2d[0];     // per-view sink of the caller (train.py:159): never accumulated
     o.dL_dmeans2D[3 * (size_t)idx + 1] = dmean2d[1];
     o.dL_dmeans2D[3 * (size_t)idx + 2] = 0.f;
-    o.dL_dopacity[idx] = dopac;
+    if (o.dL_dconic)
+        reinterpret_cast<float4*>(o.dL_dconic)[idx] = make_float4(dconic[0], dconic[1], 0.f, dconic[2]);
+    if (accum && !vis) return;
+    auto put = [accum](float* p, float v) { *p = accum ? *p + v : v; };
+    auto put4 = [accum](float4* p, float4 v) {
+        if (accum) { const float4 c = *p; v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w; }
+        *p = v;
+    };
+    put(o.dL_dopacity + idx, dopac);
 #pragma unroll
-    for (int k = 0; k < 3; k++) o.dL_dmeans3D[3 * (size_t)idx + k] = dmean[k];
+    for (int k = 0; k < 3; k++) put(o.dL_dmeans3D + 3 * (size_t)idx + k, dmean[k]);
     if (o.dL_dcolors) {
 #pragma unroll
-        for (int k = 0; k < 3; k++) o.dL_dcolors[3 * (size_t)idx + k] = dcolor[k];
+        for (int k = 0; k < 3; k++) put(o.dL_dcolors + 3 * (size_t)idx + k, dcolor[k]);
     }
     if (o.dL_dcov3D) {
 #pragma unroll
-        for (int k = 0; k < 6; k++) o.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+        for (int k = 0; k < 6; k++) put(o.dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
     }
-    if (o.dL_dconic)
-        reinterpret_cast<float4*>(o.dL_dconic)[idx] = make_float4(dconic[0], dconic[1], 0.f, dconic[2]);
     if (o.dL_dscales) {
 #pragma unroll
-        for (int k = 0; k < 3; k++) o.dL_dscales[3 * (size_t)idx + k] = dscale[k];
+        for (int k = 0; k < 3; k++) put(o.dL_dscales + 3 * (size_t)idx + k, dscale[k]);
     }
-    if (o.dL_drotations) reinterpret_cast<float4*>(o.dL_drotations)[idx] = make_float4(drot[0], drot[1], drot[2], drot[3]);
+    if (o.dL_drotations) put4(reinterpret_cast<float4*>(o.dL_drotations) + idx, make_float4(drot[0], drot[1], drot[2], drot[3]));
     if (o.dL_dsh) {
         if (SH16) {
             float f[48];
@@ -544,13 +552,16 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b)
                 f[3 * k] = sh_coef[k] * dRGB[0]; f[3 * k + 1] = sh_coef[k] * dRGB[1]; f[3 * k + 2] = sh_coef[k] * dRGB[2];
             }
             float4* dst = reinterpret_cast<float4*>(o.dL_dsh + (size_t)idx * 48);
+            // coefficients above the active degree have zero gradient: in accumulate mode they need no traffic at all
+            const int nq = accum ? ((a.D + 1) * (a.D + 1) * 3 + 3) / 4 : 12;
 #pragma unroll
-            for (int k = 0; k < 12; k++) dst[k] = make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]);
+            for (int k = 0; k < 12; k++)
+                if (k < nq) put4(dst + k, make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]));
         } else {
             float* dst = o.dL_dsh + (size_t)idx * M * 3;
             for (int k = 0; k < M; k++) {
                 const float c = k < 16 ? sh_coef[k < 16 ? k : 0] : 0.f;
-                dst[3 * k] = c * dRGB[0]; dst[3 * k + 1] = c * dRGB[1]; dst[3 * k + 2] = c * dRGB[2];
+                put(dst + 3 * k, c * dRGB[0]); put(dst + 3 * k + 1, c * dRGB[1]); put(dst + 3 * k + 2, c * dRGB[2]);
             }
         }
     }

@@ -23,7 +23,7 @@ class _View(C.Structure):
 
 class _Grads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("dL_dmeans2D", "dL_dopacity", "dL_dmeans3D", "dL_dcolors", "dL_dcov3D",
-                                          "dL_dsh", "dL_dscales", "dL_drotations", "dL_dconic")]
+                                          "dL_dsh", "dL_dscales", "dL_drotations", "dL_dconic")] + [("accumulate", C.c_int)]
 
 
 _ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
@@ -89,6 +89,20 @@ def _ptr(t):
     return None if t is None or t.numel() == 0 else t.data_ptr()
 
 
+def _round_capacity(nbytes):
+    """Scratch sizes follow num_rendered, which changes from view to view; rounding large requests up to
+    {1, 1.25, 1.5, 1.75} x 2^k keeps them within a handful of size classes, so torch's caching allocator serves them
+    from its pool instead of calling cudaMalloc (a device-wide stall) for every new camera."""
+    if nbytes <= (1 << 20):
+        return nbytes
+    k = nbytes.bit_length() - 1
+    for m in (4, 5, 6, 7, 8):
+        c = (m << k) >> 2
+        if c >= nbytes:
+            return c
+    return nbytes
+
+
 class _Scratch:
     """The three resizable byte buffers of rasterize_points.cu:68-78, handed out through callbacks."""
 
@@ -100,7 +114,7 @@ class _Scratch:
         def make(key):
             def cb(_ctx, nbytes):
                 try:
-                    t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+                    t = torch.empty(_round_capacity(int(nbytes)), dtype=torch.uint8, device=self.device)
                     self.bufs[key] = t
                     return t.data_ptr()
                 except Exception as ex:   # surfaces as GSR_E_ALLOC, re-raised by the caller
@@ -166,10 +180,14 @@ def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_m
 def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
                                  degree, campos, geomBuffer, R, binningBuffer, imageBuffer, antialiasing, debug,
-                                 want_conic=False):
+                                 want_conic=False, grad_sinks=None):
     """rasterize_points.cu:117-196. Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
     dL_dscales, dL_drotations); gradients of inputs that were not supplied are None. With want_conic=True a 9th
-    tensor dL_dconic[P,2,2] is appended (parity tests)."""
+    tensor dL_dconic[P,2,2] is appended (parity tests).
+    grad_sinks (superset, multi-view batches): dict of fp32 contiguous CUDA tensors keyed by input name ("means3D",
+    "opacities", "shs" | "colors_precomp", "scales" + "rotations" | "cov3D_precomp"), one for EVERY supplied input. The
+    gradients of this view are then ADDED into them inside the kernel (gsr_grads.accumulate) and the corresponding
+    returned entries are None; dL_dmeans2D is still returned per view."""
     P = int(means3D.size(0))
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     dev = means3D.device
@@ -179,18 +197,32 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
                           projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, False, debug, antialiasing, keep)
         M = view.M
         f = dict(dtype=torch.float32, device=dev)
-        dL_dmeans3D = torch.empty((P, 3), **f)
         dL_dmeans2D = torch.empty((P, 3), **f)
-        dL_dopacity = torch.empty((P, 1), **f)
-        dL_dcolors = torch.empty((P, 3), **f) if colors.numel() != 0 else None
-        dL_dcov3D = torch.empty((P, 6), **f) if cov3D_precomp.numel() != 0 else None
-        dL_dsh = torch.empty((P, M, 3), **f) if sh.numel() != 0 else None
-        dL_dscales = torch.empty((P, 3), **f) if scales.numel() != 0 else None
-        dL_drot = torch.empty((P, 4), **f) if rotations.numel() != 0 else None
         dL_dconic = torch.empty((P, 2, 2), **f) if want_conic else None
+        shapes = dict(means3D=(P, 3), opacities=(P, 1), colors_precomp=(P, 3) if colors.numel() != 0 else None,
+                      cov3D_precomp=(P, 6) if cov3D_precomp.numel() != 0 else None,
+                      shs=(P, M, 3) if sh.numel() != 0 else None, scales=(P, 3) if scales.numel() != 0 else None,
+                      rotations=(P, 4) if rotations.numel() != 0 else None)
+        if grad_sinks is None:
+            o = {k: (torch.empty(shp, **f) if shp is not None else None) for k, shp in shapes.items()}
+        else:
+            o = {}
+            for k, shp in shapes.items():
+                if shp is None:
+                    o[k] = None
+                    continue
+                t = grad_sinks.get(k)
+                if t is None:
+                    raise RuntimeError(f"grad_sinks: no sink for supplied input '{k}' (accumulation is all-or-nothing)")
+                if (not t.is_cuda or t.device != dev or t.dtype != torch.float32 or not t.is_contiguous()
+                        or t.numel() != torch.Size(shp).numel()):
+                    raise RuntimeError(f"grad_sinks['{k}'] must be a contiguous fp32 tensor of {shp} on {dev}")
+                o[k] = t
+        dL_dmeans3D, dL_dopacity, dL_dcolors, dL_dcov3D = o["means3D"], o["opacities"], o["colors_precomp"], o["cov3D_precomp"]
+        dL_dsh, dL_dscales, dL_drot = o["shs"], o["scales"], o["rotations"]
         if P != 0:
             g = _Grads(_ptr(dL_dmeans2D), _ptr(dL_dopacity), _ptr(dL_dmeans3D), _ptr(dL_dcolors), _ptr(dL_dcov3D),
-                       _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot), _ptr(dL_dconic))
+                       _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot), _ptr(dL_dconic), 0 if grad_sinks is None else 1)
             dpix = _f32(dL_dout_color)
             dinv = _f32(dL_dout_invdepth) if dL_dout_invdepth is not None else None
             acc = torch.empty(int(lib().gsr_backward_scratch_bytes(P)), dtype=torch.uint8, device=dev)
@@ -198,6 +230,8 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
                                     _ptr(imageBuffer), dpix.data_ptr(), _ptr(dinv), acc.data_ptr(), C.byref(g),
                                     torch.cuda.current_stream(dev).cuda_stream)
             _check(rc, "gsr_backward")
+    if grad_sinks is not None:
+        dL_dcolors = dL_dopacity = dL_dmeans3D = dL_dcov3D = dL_dsh = dL_dscales = dL_drot = None
     out = (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drot)
     return out + (dL_dconic,) if want_conic else out
 

