@@ -48,8 +48,9 @@ static inline T* carve(char*& p, size_t count) {
 #define GSR_SCAN_TILE 2048    // items per scan tile (256 threads x 8)
 
 static inline size_t sort_tiles(size_t n) { return (n + GSR_SORT_TILE - 1) / GSR_SORT_TILE; }
-// scratch words for radix_sort_u32 over n items: per-pass digit totals + the [256][tiles] table
-static inline size_t sort_scratch_words(size_t n) { return 8 * GSR_RADIX + GSR_RADIX * sort_tiles(n) + 64; }
+// scratch words for radix_sort_u32 over n items: digit histograms [4][256], tickets, and one look-back status
+// word per (pass, tile, digit)
+static inline size_t sort_scratch_words(size_t n) { return 4 * GSR_RADIX + 64 + 4 * GSR_RADIX * sort_tiles(n) + 64; }
 
 struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46)
     float* depths;            // [P] view-space z (visible Gaussians only)

@@ -1,4 +1,4 @@
-// gsr_sort.cu -- hand-written stable LSD radix sort for (u32 key, u32 value) pairs, 8-bit digits.
+// gsr_sort.cu -- hand-written stable LSD radix sort for (u32 key, u32 value) pairs, 8-bit digits, onesweep style.
 //
 // Replaces cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:303-308, simple_knn.cu:211-214).
 // The rasterizer no longer sorts 64-bit (tile|depth) keys over all R instances (6 passes of 24 B).
@@ -6,12 +6,16 @@
 // order, and then needs only a stable sort by tile id (2 passes at 1080p) -- same final order as
 // the reference's 45-bit sort, ~4x fewer bytes moved ("Binning").
 //
-// Per pass, three launches, no spinning and no inter-block waits (deterministic, hang-free):
-//   digit_hist   : per sort-tile (4096 keys) digit counts -> table[digit][tile], totals[digit]
-//   digit_scan   : block d: base(d) = sum totals[<d]; exclusive scan of row d in place
-//   digit_scatter: re-rank the tile's keys stably (warp match + per-warp counters), reorder them in
-//                  shared memory so that equal digits are contiguous, write coalesced runs.
-// HBM bytes per pass and item: 4 (hist) + 8 (load) + 8 (store) = 20; the last pass may skip keys.
+// Launches per sort: one memset (histograms, tickets, look-back status), ONE histogram kernel for the digits
+// of every pass, then ONE kernel per pass:
+//   * a tile of 4096 pairs per CTA, handed out by an atomic ticket (so a CTA only ever waits for tiles whose
+//     CTAs are already resident: the look-back cannot dead-lock);
+//   * stable ranks from per-bit ballots + per-warp shared counters (no block-wide atomics);
+//   * the tile's per-digit totals are published, the pairs are reordered in shared memory, and the global
+//     position of each digit run comes from a decoupled look-back over the predecessors' status words
+//     (flag + value in one 32-bit word, relaxed gpu-scope accesses);
+//   * runs are written out coalesced.
+// HBM bytes per pair: 4 (histogram, once) + 16 per pass (read 8, write 8).
 #include "gsr_common.cuh"
 
 namespace gsr {
@@ -19,85 +23,115 @@ namespace gsr {
 constexpr int kSortThreads = 256;
 constexpr int kSortItems = GSR_SORT_TILE / kSortThreads;   // 16
 constexpr int kSortWarps = kSortThreads / 32;               // 8
+constexpr uint32_t kFlagAgg = 1u << 30, kFlagInc = 2u << 30, kValMask = (1u << 30) - 1u;
+constexpr unsigned kAll = 0xffffffffu;
+constexpr int kHistCopies = 8;
 
-__global__ void __launch_bounds__(kSortThreads) digit_hist_kernel(const uint32_t* __restrict__ keys, int n, int shift,
-                                                                   uint32_t mask, uint32_t* __restrict__ table,
-                                                                   uint32_t* __restrict__ totals, int tiles) {
-    __shared__ uint32_t hist[GSR_RADIX];
-    const int tile = blockIdx.x;
-    hist[threadIdx.x] = 0;
-    __syncthreads();
-    const int base = tile * GSR_SORT_TILE;
+// lanes of the warp holding the same 8-bit digit as this lane (valid lanes only): 8 ballots, one per bit.
+// (MATCH.ANY does this in one instruction but measured ~48 cycles per warp-instruction per SM on B200.)
+__device__ __forceinline__ uint32_t same_digit_lanes(uint32_t d, bool ok) {
+    uint32_t peers = __ballot_sync(kAll, ok);
 #pragma unroll
-    for (int i = 0; i < kSortItems; i++) {
-        const int idx = base + i * kSortThreads + threadIdx.x;
-        if (idx < n) atomicAdd(&hist[(__ldg(keys + idx) >> shift) & mask], 1u);
+    for (int b = 0; b < 8; b++) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t bal = __ballot_sync(kAll, bit);
+        peers &= bit ? bal : ~bal;
     }
-    __syncthreads();
-    const uint32_t c = hist[threadIdx.x];
-    table[(size_t)threadIdx.x * tiles + tile] = c;
-    if (c) atomicAdd(&totals[threadIdx.x], c);
+    return peers;
 }
 
-// grid = 256 blocks (one per digit), 256 threads
-__global__ void __launch_bounds__(256) digit_scan_kernel(uint32_t* __restrict__ table, const uint32_t* __restrict__ totals,
-                                                          int tiles) {
-    __shared__ uint32_t warp_sums[8];
-    __shared__ uint32_t s_carry;
-    const int d = blockIdx.x, t = threadIdx.x, lane = t & 31, w = t >> 5;
-    // base = sum of totals of smaller digits
-    uint32_t v = (t < d) ? totals[t] : 0u;
+__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// exclusive scan of one value per thread over the 256 threads of the CTA
+__device__ __forceinline__ uint32_t block_excl_scan256(uint32_t v, uint32_t* warp_sums) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t incl = v;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) warp_sums[w] = v;
-    __syncthreads();
-    if (t == 0) {
-        uint32_t b = 0;
-        for (int i = 0; i < 8; i++) b += warp_sums[i];
-        s_carry = b;
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(kAll, incl, o);
+        if (lane >= o) incl += y;
     }
+    if (lane == 31) warp_sums[w] = incl;
     __syncthreads();
-    uint32_t* row = table + (size_t)d * tiles;
-    for (int c0 = 0; c0 < tiles; c0 += 256) {
-        const int i = c0 + t;
-        const uint32_t x = (i < tiles) ? row[i] : 0u;
-        uint32_t incl = x;
+    uint32_t woff = 0;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += y;
+    for (int k = 0; k < kSortWarps; k++)
+        if (k < w) woff += warp_sums[k];
+    __syncthreads();
+    return woff + incl - v;
+}
+
+// ------------------------------------------------------------------ digit histograms of every pass, one read of the keys
+__global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const uint32_t* __restrict__ keys, int n, int passes,
+                                                                   int total_bits, uint32_t* __restrict__ ghist) {
+    // kHistCopies replicas per digit, picked by lane: depth exponents put most keys of a warp into a few digits of
+    // the top byte, and same-address shared atomics serialise (MATCH.ANY aggregation measured slower than this)
+    __shared__ uint32_t sh[4][kHistCopies][GSR_RADIX];
+    const int t = threadIdx.x, lane = t & 31, cp = lane & (kHistCopies - 1);
+    for (int i = t; i < 4 * kHistCopies * GSR_RADIX; i += kSortThreads) (&sh[0][0][0])[i] = 0;
+    __syncthreads();
+    const int nvec = n >> 2;                                       // keys is 128-byte aligned (carved scratch)
+    const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+    const int stride = gridDim.x * kSortThreads;
+    for (int i = blockIdx.x * kSortThreads + t; i < nvec; i += stride) {
+        const uint4 v = __ldg(k4 + i);
+        const uint32_t kk[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            for (int p = 0; p < passes; p++) {
+                const int bits = min(8, total_bits - 8 * p);
+                atomicAdd(&sh[p][cp][(kk[j] >> (8 * p)) & ((1u << bits) - 1u)], 1u);
+            }
         }
-        if (lane == 31) warp_sums[w] = incl;
-        __syncthreads();
-        uint32_t woff = 0;
-        for (int k = 0; k < w; k++) woff += warp_sums[k];
-        const uint32_t carry = s_carry;
-        if (i < tiles) row[i] = carry + woff + incl - x;
-        __syncthreads();
-        if (t == 255) s_carry = carry + woff + incl;
-        __syncthreads();
+    }
+    if (blockIdx.x == 0 && t < (n & 3)) {                          // tail (< 4 keys)
+        const uint32_t k = __ldg(keys + (nvec << 2) + t);
+        for (int p = 0; p < passes; p++) {
+            const int bits = min(8, total_bits - 8 * p);
+            atomicAdd(&sh[p][0][(k >> (8 * p)) & ((1u << bits) - 1u)], 1u);
+        }
+    }
+    __syncthreads();
+    for (int p = 0; p < passes; p++) {
+        uint32_t c = 0;
+#pragma unroll
+        for (int k = 0; k < kHistCopies; k++) c += sh[p][k][t];
+        if (c) atomicAdd(&ghist[p * GSR_RADIX + t], c);
     }
 }
 
+// ------------------------------------------------------------------ one pass
 template <bool WRITE_KEYS>
-__global__ void __launch_bounds__(kSortThreads) digit_scatter_kernel(const uint32_t* __restrict__ keys_in,
-                                                                      const uint32_t* __restrict__ vals_in,
-                                                                      uint32_t* __restrict__ keys_out,
-                                                                      uint32_t* __restrict__ vals_out, int n, int shift,
-                                                                      uint32_t mask, const uint32_t* __restrict__ table,
-                                                                      int tiles) {
-    __shared__ uint32_t whist[kSortWarps][GSR_RADIX + 1];   // per-warp digit counters, then warp offsets
-    __shared__ uint32_t dstart[GSR_RADIX + 1];              // local start of each digit's run
-    __shared__ uint32_t gbase[GSR_RADIX];                   // global start of this tile's run per digit
+__global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_t* __restrict__ keys_in,
+                                                                 const uint32_t* __restrict__ vals_in,
+                                                                 uint32_t* __restrict__ keys_out,
+                                                                 uint32_t* __restrict__ vals_out, int n, int shift,
+                                                                 uint32_t mask, const uint32_t* __restrict__ ghist,
+                                                                 uint32_t* __restrict__ ticket,
+                                                                 uint32_t* __restrict__ status) {
+    __shared__ uint32_t whist[kSortWarps][GSR_RADIX];   // per-warp digit counters, then exclusive warp offsets
+    __shared__ uint32_t dstart[GSR_RADIX];              // local start of each digit's run
+    __shared__ uint32_t gofs[GSR_RADIX];                // global start of the run minus its local start
     __shared__ uint32_t s_keys[GSR_SORT_TILE];
     __shared__ uint32_t s_vals[GSR_SORT_TILE];
     __shared__ uint32_t warp_sums[kSortWarps];
-    const int tile = blockIdx.x, t = threadIdx.x, lane = t & 31, w = t >> 5;
+    __shared__ uint32_t s_tile;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    if (t == 0) s_tile = atomicAdd(ticket, 1u);
+#pragma unroll
+    for (int k = 0; k < kSortWarps; k++) whist[k][t] = 0;
+    __syncthreads();
+    const int tile = (int)s_tile;
     const int base = tile * GSR_SORT_TILE;
     const int count = min(GSR_SORT_TILE, n - base);
-    for (int i = t; i < kSortWarps * (GSR_RADIX + 1); i += kSortThreads) (&whist[0][0])[i] = 0;
-    gbase[t] = table[(size_t)t * tiles + tile];
-    __syncthreads();
+    const uint32_t gbase = block_excl_scan256(__ldg(ghist + t), warp_sums);   // first output slot of digit t
 
     // warp-striped load: order index inside the tile = w*512 + i*32 + lane
     uint32_t key[kSortItems], val[kSortItems], rank[kSortItems];
@@ -113,17 +147,17 @@ __global__ void __launch_bounds__(kSortThreads) digit_scatter_kernel(const uint3
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
         const int idx = wbase + i * 32 + lane;
-        const uint32_t d = (idx < n) ? ((key[i] >> shift) & mask) : GSR_RADIX;   // 256 = "not an item"
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const uint32_t lower = __popc(peers & lt_mask);
-        const uint32_t prev = whist[w][d];
-        rank[i] = prev + lower;
-        __syncwarp();
-        if (lower == 0) whist[w][d] = prev + __popc(peers);
-        __syncwarp();
+        const bool ok = idx < n;
+        const uint32_t d = (key[i] >> shift) & mask;
+        const uint32_t peers = same_digit_lanes(d, ok);            // invalid lanes are in nobody's set (but their own)
+        const int leader = ok ? __ffs(peers) - 1 : lane;
+        uint32_t prev = 0;
+        if (ok && lane == leader) prev = atomicAdd(&whist[w][d], (uint32_t)__popc(peers));   // same warp: program order
+        prev = __shfl_sync(kAll, prev, leader);
+        rank[i] = prev + __popc(peers & lt_mask);
     }
     __syncthreads();
-    // digit t: exclusive scan over warps; block count
+    // digit t: exclusive scan over the warps, tile total
     uint32_t run = 0;
 #pragma unroll
     for (int k = 0; k < kSortWarps; k++) {
@@ -131,21 +165,12 @@ __global__ void __launch_bounds__(kSortThreads) digit_scatter_kernel(const uint3
         whist[k][t] = run;
         run += c;
     }
-    // exclusive scan over digits -> dstart
-    uint32_t incl = run;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += y;
-    }
-    if (lane == 31) warp_sums[w] = incl;
+    uint32_t* my_status = status + (size_t)tile * GSR_RADIX + t;
+    st_relaxed(my_status, (tile == 0 ? kFlagInc : kFlagAgg) | run);            // publish early: successors can proceed
+    const uint32_t ds = block_excl_scan256(run, warp_sums);
+    dstart[t] = ds;
     __syncthreads();
-    uint32_t woff = 0;
-    for (int k = 0; k < w; k++) woff += warp_sums[k];
-    dstart[t] = woff + incl - run;
-    if (t == 255) dstart[GSR_RADIX] = woff + incl;
-    __syncthreads();
-    // place into shared memory at the local sorted position
+    // reorder inside shared memory
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
         const int idx = wbase + i * 32 + lane;
@@ -156,6 +181,22 @@ __global__ void __launch_bounds__(kSortThreads) digit_scatter_kernel(const uint3
             s_vals[lp] = val[i];
         }
     }
+    // decoupled look-back for digit t
+    uint32_t excl = 0;
+    if (tile > 0) {
+        for (int j = tile - 1;; --j) {
+            const uint32_t* ps = status + (size_t)j * GSR_RADIX + t;
+            uint32_t s = ld_relaxed(ps);
+            while ((s >> 30) == 0u) {
+                __nanosleep(32);
+                s = ld_relaxed(ps);
+            }
+            excl += s & kValMask;
+            if ((s >> 30) == 2u) break;
+        }
+        st_relaxed(my_status, kFlagInc | (excl + run));
+    }
+    gofs[t] = gbase + excl - ds;
     __syncthreads();
     // coalesced runs out
 #pragma unroll
@@ -163,8 +204,7 @@ __global__ void __launch_bounds__(kSortThreads) digit_scatter_kernel(const uint3
         const int slot = i * kSortThreads + t;
         if (slot < count) {
             const uint32_t k = s_keys[slot];
-            const uint32_t d = (k >> shift) & mask;
-            const uint32_t pos = gbase[d] + (slot - dstart[d]);
+            const uint32_t pos = gofs[(k >> shift) & mask] + (uint32_t)slot;
             if (WRITE_KEYS) keys_out[pos] = k;
             vals_out[pos] = s_vals[slot];
         }
@@ -177,20 +217,22 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
     if (n <= 0 || total_bits <= 0) return 0;
     const int passes = radix_passes(total_bits);
     const int tiles = (int)sort_tiles((size_t)n);
-    uint32_t* totals = scratch;                 // [8][256]
-    uint32_t* table = scratch + 8 * GSR_RADIX;  // [256][tiles]
-    cudaError_t e = cudaMemsetAsync(totals, 0, sizeof(uint32_t) * 8 * GSR_RADIX, s);
-    if (e != cudaSuccess) return (int)e;
+    uint32_t* ghist = scratch;                                  // [4][256]
+    uint32_t* tickets = scratch + 4 * GSR_RADIX;                // [4] (+ padding)
+    uint32_t* status = scratch + 4 * GSR_RADIX + 64;            // [passes][tiles][256]
+    GSR_MEMSET("memset_sort", s, scratch, 0, sizeof(uint32_t) * (4 * GSR_RADIX + 64 + (size_t)passes * tiles * GSR_RADIX));
+    const int hist_blocks = min((n / 4 + kSortThreads - 1) / kSortThreads, 148 * 8);
+    GSR_LAUNCH("radix_hist", debug, s,
+               (radix_hist_kernel<<<hist_blocks > 0 ? hist_blocks : 1, kSortThreads, 0, s>>>(ka, n, passes, total_bits, ghist)));
     uint32_t *kin = ka, *vin = va, *kout = kb, *vout = vb;
     for (int p = 0; p < passes; p++) {
         const int shift = 8 * p;
         const int bits = (total_bits - shift) < 8 ? (total_bits - shift) : 8;
         const uint32_t mask = (1u << bits) - 1u;
-        GSR_LAUNCH("digit_hist", debug, s,
-                   (digit_hist_kernel<<<tiles, kSortThreads, 0, s>>>(kin, n, shift, mask, table, totals + p * GSR_RADIX, tiles)));
-        GSR_LAUNCH("digit_scan", debug, s, (digit_scan_kernel<<<GSR_RADIX, 256, 0, s>>>(table, totals + p * GSR_RADIX, tiles)));
-        GSR_LAUNCH("digit_scatter", debug, s,
-                   (digit_scatter_kernel<true><<<tiles, kSortThreads, 0, s>>>(kin, vin, kout, vout, n, shift, mask, table, tiles)));
+        GSR_LAUNCH("onesweep_pass", debug, s,
+                   (onesweep_kernel<true><<<tiles, kSortThreads, 0, s>>>(kin, vin, kout, vout, n, shift, mask,
+                                                                         ghist + p * GSR_RADIX, tickets + p,
+                                                                         status + (size_t)p * tiles * GSR_RADIX)));
         uint32_t* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
     }
