@@ -60,14 +60,31 @@ def parse_args():
 
 # ----------------------------------------------------------------------------------------------- clocks
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """SM clock / power / throttle reasons sampled every 100 ms WHILE the timed region runs. NVML in a thread (set up
+    before the warm-up, so nothing is forked or initialised inside the region); nvidia-smi -lms as the fallback."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.nv, self.h = index, [], None, None, None
+        self.stop_flag = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].strip().isdigit() else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv = pynvml
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
 
     def start(self):
+        self.stop_flag.clear()
+        if self.nv is not None:
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
@@ -77,19 +94,38 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        nv = self.nv
+        R = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+             "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self.stop_flag.is_set():
+            try:
+                sm = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.rows.append([str(sm), str(self.sm_max), str(pw)] + ["Active" if bits & R[k] else "Not Active" for k in
+                                 ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.1)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
-        if self.proc is None:
+        self.stop_flag.set()
+        if self.nv is not None:
+            self.t.join(timeout=1.0)
+        elif self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.25)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
+        else:
+            time.sleep(0.25)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
         sm, mx, reasons, pw = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
@@ -104,7 +140,8 @@ class ClockSampler:
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons),
+                "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
 # ----------------------------------------------------------------------------------------------- workload
@@ -332,6 +369,23 @@ def cpu_baseline(args):
 
 # ----------------------------------------------------------------------------------------------- main
 def main():
+    # Libraries (NCCL prints its version banner) must not leak into the one-JSON-line contract: fd 1 goes to stderr
+    # for the whole run and the result line is written to the saved descriptor at the end.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        return _main(real_stdout)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+
+
+def emit(fd, obj):
+    os.write(fd, (json.dumps(obj) + "\n").encode())
+
+
+def _main(out_fd):
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -343,7 +397,7 @@ def main():
     if not torch.cuda.is_available():
         if args.impl == "reference":
             cb = cpu_baseline(args)
-            print(json.dumps({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "views/s", "n_gpus": 0,
+            emit(out_fd, ({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "views/s", "n_gpus": 0,
                               "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "cpu_baseline": cb,
                               "e2e": {"value": cb["value"], "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
             return 0
@@ -361,7 +415,7 @@ def main():
         from oracle import ref_cuda
         if not ref_cuda.available():
             cb = cpu_baseline(args)
-            print(json.dumps({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "views/s", "n_gpus": 1,
+            emit(out_fd, ({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "views/s", "n_gpus": 1,
                               "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "cpu_baseline": cb,
                               "ms_per_step": None, "config": {"workload": "C3 (CPU port: reference CUDA build absent)"},
                               "e2e": {"value": cb["value"], "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
@@ -375,18 +429,23 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    last_step_ms = []
+
     def timed(fn, steps, prof=False):
         """K steps bracketed by barrier + synchronize on both sides; device time by CUDA events, max over ranks."""
         barrier()
         if prof:
             arm._C.profile_enable(True)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
         t0 = time.perf_counter()
         e0.record()
-        for _ in range(steps):
+        for i in range(steps):
             fn()
+            marks[i].record()
         e1.record()
         barrier()
+        last_step_ms[:] = [a.elapsed_time(b) for a, b in zip([e0] + marks[:-1], marks)]
         wall = (time.perf_counter() - t0) * 1e3
         if prof:
             arm._C.profile_enable(False)
@@ -395,6 +454,7 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms[0]), float(ms[1])
 
+    sampler = ClockSampler(local) if rank == 0 else None
     # warm-up: at least W steps, then until the step time has settled (the caching allocator needs a few different
     # num_rendered sizes before it stops calling cudaMalloc) -- at most 24 steps
     warm_run, prev = 0, None
@@ -416,11 +476,11 @@ def main():
 
     prof = args.impl == "ours" and not args.no_kernel_timing
     l0 = arm.launches()
-    sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms_total, _wall = timed(arm.step, args.steps)
     launches = arm.launches() - l0
+    step_ms = sorted(last_step_ms)
     # per-kernel device times: the same K steps again with one CUDA-event pair around every launch. Kept out of the
     # headline region because ~60 event records per view cost the host ~5 % there; kernel durations are unaffected.
     ms_prof = timed(arm.step, args.steps, prof=True)[0] if prof else None
@@ -486,6 +546,7 @@ def main():
                           "parallelism": f"view-parallel dp{ref_world}, replicated Gaussians" +
                                          (", NCCL all-reduce of 59 floats/Gaussian per step" if ref_world > 1 else ""),
                           "l2": "inputs (708 MB parameters + 300 MB scratch per view) exceed the 126 MB L2; no explicit flush"},
+               "step_ms_min_med_max": [round(step_ms[0], 3), round(step_ms[len(step_ms) // 2], 3), round(step_ms[-1], 3)],
                "clocks": clocks, "gpu_launches": launches,
                "kernel_timing_pass_ms_per_step": round(ms_prof / args.steps, 3) if ms_prof else None}
         if args.impl == "reference":
@@ -502,7 +563,7 @@ def main():
             out["cpu_baseline"] = cb
             out["workload_stats"] = stats
             out["kernels"] = kernels
-        print(json.dumps(out))
+        emit(out_fd, out)
     if ref_world > 1:
         dist.destroy_process_group()
     return 0

@@ -118,8 +118,10 @@ __device__ __forceinline__ void rect_of(float px, float py, int max_radius, int 
     y1 = min(gy, max((int)0, (int)((py + max_radius + GSR_TILE - 1) / GSR_TILE)));
 }
 
-constexpr int kDupSerialMax = 12;   // rects up to this many tiles are written by their own thread
-
+// One warp emits the instances of 32 consecutive Gaussians (depth order). Their output slots are one contiguous
+// range, so the lanes walk that range 32 slots at a time -- fully coalesced stores -- and find the owner of their
+// slot by a 5-step binary search over the lanes' end offsets (shuffles). Replaces the thread-serial, divergent loop of
+// duplicateWithKeys (rasterizer_impl.cu:88-109): a warp-store there touches 32 different sectors.
 __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint32_t* __restrict__ order,
                                                               const uint32_t* __restrict__ tiles_touched,
                                                               const uint32_t* __restrict__ offsets,
@@ -129,58 +131,73 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint32
                                                               uint32_t* __restrict__ vals) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    uint32_t g = 0, n = 0, off = 0;
-    int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    uint32_t g = 0, n = 0, end = 0;
+    int x0 = 0, y0 = 0, bw = 1;
     if (j < P) {
         g = __ldg(order + j);
         n = __ldg(tiles_touched + g);
+        end = __ldg(offsets + j);                   // inclusive scan in depth order
         if (n > 0) {
-            off = __ldg(offsets + j) - n;
+            int x1, y1;
             const float4 r0 = __ldg(rec + 3 * (size_t)g);
             rect_of(r0.x, r0.y, __ldg(radii + g), gx, gy, x0, y0, x1, y1);
+            bw = x1 - x0;
         }
     }
-    if (n > 0 && n <= kDupSerialMax) {
-        for (int y = y0; y < y1; y++)
-            for (int x = x0; x < x1; x++) {
-                tile_keys[off] = (uint32_t)(y * gx + x);
-                vals[off] = g;
-                off++;
-            }
-    }
-    // large rectangles: the whole warp writes them, one rectangle at a time
-    uint32_t big = __ballot_sync(0xffffffffu, n > kDupSerialMax);
-    while (big) {
-        const int src = __ffs(big) - 1;
-        big &= big - 1;
-        const uint32_t bg = __shfl_sync(0xffffffffu, g, src);
-        const uint32_t bn = __shfl_sync(0xffffffffu, n, src);
-        const uint32_t boff = __shfl_sync(0xffffffffu, off, src);
-        const int bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
-        const int bw = __shfl_sync(0xffffffffu, x1, src) - bx0;
-        for (uint32_t k = lane; k < bn; k += 32) {
-            const int y = by0 + (int)(k / (uint32_t)bw), x = bx0 + (int)(k % (uint32_t)bw);
-            tile_keys[boff + k] = (uint32_t)(y * gx + x);
-            vals[boff + k] = bg;
+    // culled Gaussians sort to the end (key 0xFFFFFFFF): whole warps of them leave here
+    if (__ballot_sync(0xffffffffu, n > 0) == 0u) return;
+    // lanes beyond P: end = end of the last valid lane so the search never selects them
+    const uint32_t last_end = __shfl_sync(0xffffffffu, end, min(31, P - 1 - (j - lane)));
+    if (j >= P) end = last_end;
+    const uint32_t first = __shfl_sync(0xffffffffu, end - n, 0);
+    const float inv_bw = 1.0f / (float)bw;
+    for (uint32_t s = first + lane; __any_sync(0xffffffffu, s < last_end); s += 32) {
+        // owner = number of lanes whose range ends at or before s
+        int lo = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            const uint32_t e = __shfl_sync(0xffffffffu, end, lo + step - 1);
+            if (e <= s) lo += step;
+        }
+        const int owner = min(lo, 31);
+        const uint32_t og = __shfl_sync(0xffffffffu, g, owner);
+        const uint32_t oend = __shfl_sync(0xffffffffu, end, owner), on = __shfl_sync(0xffffffffu, n, owner);
+        const int ox0 = __shfl_sync(0xffffffffu, x0, owner), oy0 = __shfl_sync(0xffffffffu, y0, owner);
+        const int obw = __shfl_sync(0xffffffffu, bw, owner);
+        const float oinv = __shfl_sync(0xffffffffu, inv_bw, owner);
+        if (s < last_end) {
+            const uint32_t k = s - (oend - on);                        // row-major index inside the rectangle
+            const int row = (int)(((float)k + 0.5f) * oinv);          // exact: k < 2^13, bw <= 2^7
+            const int col = (int)k - row * obw;
+            tile_keys[s] = (uint32_t)((oy0 + row) * gx + ox0 + col);
+            vals[s] = og;
         }
     }
 }
 
 // ------------------------------------------------------------------ tile ranges (A9)
+// four consecutive sorted keys per thread (one 16-byte load) + the key before them
 __global__ void __launch_bounds__(256) tile_ranges_kernel(int L, const uint32_t* __restrict__ tile_keys,
                                                            uint2* __restrict__ ranges) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= L) return;
-    const uint32_t cur = tile_keys[idx];
-    if (idx == 0) ranges[cur].x = 0;
-    else {
-        const uint32_t prev = tile_keys[idx - 1];
-        if (cur != prev) {
-            ranges[prev].y = idx;
-            ranges[cur].x = idx;
+    const int base = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (base >= L) return;
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(tile_keys) + (base >> 2));   // buffer is padded by 8 words
+    const uint32_t k[4] = {v.x, v.y, v.z, v.w};
+    uint32_t prev = base > 0 ? __ldg(tile_keys + base - 1) : 0u;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const int idx = base + q;
+        if (idx < L) {
+            const uint32_t cur = k[q];
+            if (idx == 0) ranges[cur].x = 0;
+            else if (cur != prev) {
+                ranges[prev].y = idx;
+                ranges[cur].x = idx;
+            }
+            if (idx == L - 1) ranges[cur].y = L;
+            prev = cur;
         }
     }
-    if (idx == L - 1) ranges[cur].y = L;
 }
 
 static int bits_for(uint32_t count) {   // bits needed to represent ids 0..count-1
@@ -207,7 +224,7 @@ int launch_binning(const gsr_view& v, const GeomState& g, const int* radii, Binn
     bool in_a = true;
     int e = radix_sort_u32(ka, va, kb, vb, R, tbits, b.sort_scratch, &in_a, v.debug != 0, s);
     if (e) return e;
-    GSR_LAUNCH("tile_ranges", v.debug, s, (tile_ranges_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, b.tile_keys, img.ranges)));
+    GSR_LAUNCH("tile_ranges", v.debug, s, (tile_ranges_kernel<<<(R + 1023) / 1024, 256, 0, s>>>(R, b.tile_keys, img.ranges)));
     return 0;
 }
 

@@ -27,15 +27,15 @@ constexpr uint32_t kFlagAgg = 1u << 30, kFlagInc = 2u << 30, kValMask = (1u << 3
 constexpr unsigned kAll = 0xffffffffu;
 constexpr int kHistCopies = 8;
 
-// lanes of the warp holding the same 8-bit digit as this lane (valid lanes only): 8 ballots, one per bit.
+// lanes of the warp holding the same BITS-bit digit as this lane: one ballot per bit, folded with a 3-input logic op.
 // (MATCH.ANY does this in one instruction but measured ~48 cycles per warp-instruction per SM on B200.)
-__device__ __forceinline__ uint32_t same_digit_lanes(uint32_t d, bool ok) {
-    uint32_t peers = __ballot_sync(kAll, ok);
+template <int BITS>
+__device__ __forceinline__ uint32_t same_digit_lanes(uint32_t d, uint32_t peers) {
 #pragma unroll
-    for (int b = 0; b < 8; b++) {
-        const bool bit = (d >> b) & 1u;
-        const uint32_t bal = __ballot_sync(kAll, bit);
-        peers &= bit ? bal : ~bal;
+    for (int b = 0; b < BITS; b++) {
+        const uint32_t m = 0u - ((d >> b) & 1u);                   // all ones if my bit is set
+        const uint32_t bal = __ballot_sync(kAll, m != 0u);
+        peers &= ~(bal ^ m);                                       // keep lanes whose bit equals mine
     }
     return peers;
 }
@@ -108,77 +108,66 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const uint32_t
 }
 
 // ------------------------------------------------------------------ one pass
-template <bool WRITE_KEYS>
-__global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_t* __restrict__ keys_in,
-                                                                 const uint32_t* __restrict__ vals_in,
-                                                                 uint32_t* __restrict__ keys_out,
-                                                                 uint32_t* __restrict__ vals_out, int n, int shift,
-                                                                 uint32_t mask, const uint32_t* __restrict__ ghist,
-                                                                 uint32_t* __restrict__ ticket,
-                                                                 uint32_t* __restrict__ status) {
-    __shared__ uint32_t whist[kSortWarps][GSR_RADIX];   // per-warp digit counters, then exclusive warp offsets
-    __shared__ uint32_t dstart[GSR_RADIX];              // local start of each digit's run
-    __shared__ uint32_t gofs[GSR_RADIX];                // global start of the run minus its local start
-    __shared__ uint32_t s_keys[GSR_SORT_TILE];
-    __shared__ uint32_t s_vals[GSR_SORT_TILE];
-    __shared__ uint32_t warp_sums[kSortWarps];
-    __shared__ uint32_t s_tile;
-    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
-    if (t == 0) s_tile = atomicAdd(ticket, 1u);
-#pragma unroll
-    for (int k = 0; k < kSortWarps; k++) whist[k][t] = 0;
-    __syncthreads();
-    const int tile = (int)s_tile;
-    const int base = tile * GSR_SORT_TILE;
-    const int count = min(GSR_SORT_TILE, n - base);
-    const uint32_t gbase = block_excl_scan256(__ldg(ghist + t), warp_sums);   // first output slot of digit t
+struct SortSmem {
+    uint32_t whist[kSortWarps][GSR_RADIX];   // per-warp digit counters, then local start of (warp, digit)
+    uint32_t gofs[GSR_RADIX];                // global start of the digit's run minus its local start
+    uint32_t s_keys[GSR_SORT_TILE];
+    uint32_t s_vals[GSR_SORT_TILE];
+    uint32_t warp_sums[kSortWarps];
+    uint32_t tile;
+};
 
+template <int BITS, bool FULL>
+__device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t* __restrict__ keys_in,
+                                              const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ keys_out,
+                                              uint32_t* __restrict__ vals_out, int n, int shift, int tile, uint32_t gbase,
+                                              uint32_t* __restrict__ status) {
+    constexpr uint32_t mask = (1u << BITS) - 1u;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int base = tile * GSR_SORT_TILE;
+    const int count = FULL ? GSR_SORT_TILE : n - base;
     // warp-striped load: order index inside the tile = w*512 + i*32 + lane
-    uint32_t key[kSortItems], val[kSortItems], rank[kSortItems];
-    const int wbase = base + w * (32 * kSortItems);
+    uint32_t key[kSortItems], rank[kSortItems];
+    const int wofs = w * (32 * kSortItems) + lane;
+    const uint32_t* kp = keys_in + base + wofs;
 #pragma unroll
-    for (int i = 0; i < kSortItems; i++) {
-        const int idx = wbase + i * 32 + lane;
-        const bool ok = idx < n;
-        key[i] = ok ? __ldg(keys_in + idx) : 0xFFFFFFFFu;
-        val[i] = ok ? __ldg(vals_in + idx) : 0u;
-    }
+    for (int i = 0; i < kSortItems; i++) key[i] = (FULL || wofs + i * 32 < count) ? __ldg(kp + i * 32) : 0xFFFFFFFFu;
     const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        const int idx = wbase + i * 32 + lane;
-        const bool ok = idx < n;
+        const bool ok = FULL || wofs + i * 32 < count;
         const uint32_t d = (key[i] >> shift) & mask;
-        const uint32_t peers = same_digit_lanes(d, ok);            // invalid lanes are in nobody's set (but their own)
-        const int leader = ok ? __ffs(peers) - 1 : lane;
+        const uint32_t peers = same_digit_lanes<BITS>(d, FULL ? kAll : __ballot_sync(kAll, ok));
+        const int leader = __ffs(peers) - 1;                       // invalid lanes: garbage, never used
         uint32_t prev = 0;
-        if (ok && lane == leader) prev = atomicAdd(&whist[w][d], (uint32_t)__popc(peers));   // same warp: program order
-        prev = __shfl_sync(kAll, prev, leader);
+        if (ok && lane == leader) prev = atomicAdd(&sm.whist[w][d], (uint32_t)__popc(peers));   // same warp: program order
+        prev = __shfl_sync(kAll, prev, leader & 31);
         rank[i] = prev + __popc(peers & lt_mask);
     }
     __syncthreads();
-    // digit t: exclusive scan over the warps, tile total
-    uint32_t run = 0;
+    // digit t: totals over the warps -> publish -> local start of every (warp, digit) run
+    uint32_t cnt[kSortWarps], run = 0;
 #pragma unroll
-    for (int k = 0; k < kSortWarps; k++) {
-        const uint32_t c = whist[k][t];
-        whist[k][t] = run;
-        run += c;
-    }
+    for (int k = 0; k < kSortWarps; k++) { cnt[k] = sm.whist[k][t]; run += cnt[k]; }
     uint32_t* my_status = status + (size_t)tile * GSR_RADIX + t;
     st_relaxed(my_status, (tile == 0 ? kFlagInc : kFlagAgg) | run);            // publish early: successors can proceed
-    const uint32_t ds = block_excl_scan256(run, warp_sums);
-    dstart[t] = ds;
+    const uint32_t ds = block_excl_scan256(run, sm.warp_sums);
+    uint32_t acc = ds;
+#pragma unroll
+    for (int k = 0; k < kSortWarps; k++) { sm.whist[k][t] = acc; acc += cnt[k]; }
     __syncthreads();
+    // values are only needed now: load them late so they do not occupy registers during the ranking
+    uint32_t val[kSortItems];
+    const uint32_t* vp = vals_in + base + wofs;
+#pragma unroll
+    for (int i = 0; i < kSortItems; i++) val[i] = (FULL || wofs + i * 32 < count) ? __ldg(vp + i * 32) : 0u;
     // reorder inside shared memory
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        const int idx = wbase + i * 32 + lane;
-        if (idx < n) {
-            const uint32_t d = (key[i] >> shift) & mask;
-            const uint32_t lp = dstart[d] + whist[w][d] + rank[i];
-            s_keys[lp] = key[i];
-            s_vals[lp] = val[i];
+        if (FULL || wofs + i * 32 < count) {
+            const uint32_t lp = sm.whist[w][(key[i] >> shift) & mask] + rank[i];
+            sm.s_keys[lp] = key[i];
+            sm.s_vals[lp] = val[i];
         }
     }
     // decoupled look-back for digit t
@@ -196,19 +185,46 @@ __global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_
         }
         st_relaxed(my_status, kFlagInc | (excl + run));
     }
-    gofs[t] = gbase + excl - ds;
+    sm.gofs[t] = gbase + excl - ds;
     __syncthreads();
     // coalesced runs out
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
         const int slot = i * kSortThreads + t;
-        if (slot < count) {
-            const uint32_t k = s_keys[slot];
-            const uint32_t pos = gofs[(k >> shift) & mask] + (uint32_t)slot;
-            if (WRITE_KEYS) keys_out[pos] = k;
-            vals_out[pos] = s_vals[slot];
+        if (FULL || slot < count) {
+            const uint32_t k = sm.s_keys[slot];
+            const uint32_t pos = sm.gofs[(k >> shift) & mask] + (uint32_t)slot;
+            keys_out[pos] = k;
+            vals_out[pos] = sm.s_vals[slot];
         }
     }
+}
+
+template <int BITS>
+__global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_t* __restrict__ keys_in,
+                                                                    const uint32_t* __restrict__ vals_in,
+                                                                    uint32_t* __restrict__ keys_out,
+                                                                    uint32_t* __restrict__ vals_out, int n, int shift,
+                                                                    const uint32_t* __restrict__ ghist,
+                                                                    uint32_t* __restrict__ ticket,
+                                                                    uint32_t* __restrict__ status) {
+    __shared__ SortSmem sm;
+    const int t = threadIdx.x;
+    if (t == 0) sm.tile = atomicAdd(ticket, 1u);
+#pragma unroll
+    for (int k = 0; k < kSortWarps; k++) sm.whist[k][t] = 0;
+    const uint32_t gbase = block_excl_scan256(__ldg(ghist + t), sm.warp_sums);   // first output slot of digit t (syncs)
+    const int tile = (int)sm.tile;
+    if ((tile + 1) * GSR_SORT_TILE <= n)
+        onesweep_tile<BITS, true>(sm, keys_in, vals_in, keys_out, vals_out, n, shift, tile, gbase, status);
+    else
+        onesweep_tile<BITS, false>(sm, keys_in, vals_in, keys_out, vals_out, n, shift, tile, gbase, status);
+}
+
+template <int BITS>
+static void launch_pass(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, int n, int shift,
+                        const uint32_t* ghist, uint32_t* ticket, uint32_t* status, int tiles, cudaStream_t s) {
+    onesweep_kernel<BITS><<<tiles, kSortThreads, 0, s>>>(kin, vin, kout, vout, n, shift, ghist, ticket, status);
 }
 
 int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits, uint32_t* scratch,
@@ -228,11 +244,20 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
     for (int p = 0; p < passes; p++) {
         const int shift = 8 * p;
         const int bits = (total_bits - shift) < 8 ? (total_bits - shift) : 8;
-        const uint32_t mask = (1u << bits) - 1u;
-        GSR_LAUNCH("onesweep_pass", debug, s,
-                   (onesweep_kernel<true><<<tiles, kSortThreads, 0, s>>>(kin, vin, kout, vout, n, shift, mask,
-                                                                         ghist + p * GSR_RADIX, tickets + p,
-                                                                         status + (size_t)p * tiles * GSR_RADIX)));
+        uint32_t* st = status + (size_t)p * tiles * GSR_RADIX;
+        const uint32_t* gh = ghist + p * GSR_RADIX;
+        GSR_LAUNCH("onesweep_pass", debug, s, {
+            switch (bits) {
+                case 1: launch_pass<1>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 2: launch_pass<2>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 3: launch_pass<3>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 4: launch_pass<4>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 5: launch_pass<5>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 6: launch_pass<6>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 7: launch_pass<7>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                default: launch_pass<8>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+            }
+        });
         uint32_t* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
     }

@@ -103,18 +103,74 @@ def _round_capacity(nbytes):
     return nbytes
 
 
+_pool = {}          # (device index, stream id) -> free scratch tensors
+_DEBUG_POOL = os.environ.get("GSR_DEBUG_POOL", "0") == "1"
+_POOL_MAX = 12
+
+
+class ScratchLease:
+    """Scratch blobs of one forward, checked out of a per-(device, stream) pool and handed back when the autograd
+    context that owns the lease dies (after its backward, or when the graph is dropped). The blob sizes follow
+    num_rendered, i.e. change with every camera; serving them from torch's caching allocator directly makes it
+    split and re-malloc for dozens of iterations (13 GB reserved, cudaMalloc stalls). Reuse is stream-ordered: a
+    buffer only ever goes back to the pool of the stream its forward ran on."""
+
+    def __init__(self):
+        self.key, self.bufs = None, []
+
+    def take(self, device, nbytes):
+        if self.key is None:
+            self.key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+        free = _pool.setdefault(self.key, [])
+        best = -1
+        for i, t in enumerate(free):
+            if t.numel() >= nbytes and (best < 0 or t.numel() < free[best].numel()):
+                best = i
+        if best >= 0 and free[best].numel() <= 2 * nbytes + (8 << 20):
+            t = free.pop(best)
+        else:
+            t = torch.empty(_round_capacity(nbytes), dtype=torch.uint8, device=device)
+            if _DEBUG_POOL:
+                print(f"[gsr pool] miss: want {nbytes >> 20} MiB, free {[x.numel() >> 20 for x in free]} -> new {t.numel() >> 20} MiB")
+        self.bufs.append(t)
+        return t
+
+    def release(self):
+        if self.key is not None and _pool is not None:
+            free = _pool.setdefault(self.key, [])
+            for t in self.bufs:
+                if len(free) < _POOL_MAX:
+                    free.append(t)
+        self.bufs, self.key = [], None
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+
+def empty_scratch_pool():
+    """Drops every pooled scratch buffer (the torch caching allocator gets the memory back)."""
+    _pool.clear()
+
+
 class _Scratch:
     """The three resizable byte buffers of rasterize_points.cu:68-78, handed out through callbacks."""
 
-    def __init__(self, device):
+    def __init__(self, device, lease=None):
         self.device = device
         self.bufs = {}
         self.err = None
+        self.lease = lease
 
         def make(key):
             def cb(_ctx, nbytes):
                 try:
-                    t = torch.empty(_round_capacity(int(nbytes)), dtype=torch.uint8, device=self.device)
+                    if self.lease is not None:
+                        t = self.lease.take(self.device, int(nbytes))
+                    else:
+                        t = torch.empty(_round_capacity(int(nbytes)), dtype=torch.uint8, device=self.device)
                     self.bufs[key] = t
                     return t.data_ptr()
                 except Exception as ex:   # surfaces as GSR_E_ALLOC, re-raised by the caller
@@ -126,6 +182,13 @@ class _Scratch:
     def get(self, key):
         t = self.bufs.get(key)
         return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
+
+    def close(self):
+        """The ctypes callbacks close over self: break that cycle, or the blobs (hundreds of MB) and the lease stay
+        alive until Python's cyclic collector happens to run."""
+        out = self.get("geom"), self.get("binning"), self.get("image")
+        self.cbs, self.bufs, self.lease = None, {}, None
+        return out
 
 
 def _make_view(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
@@ -151,7 +214,7 @@ def _make_view(bg, means3D, colors, opacity, scales, rotations, scale_modifier, 
 
 def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                         projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
-                        debug, antialiasing=False, want_invdepth=True):
+                        debug, antialiasing=False, want_invdepth=True, lease=None):
     """rasterize_points.cu:35-115 + superset outputs. Returns
     (num_rendered, color[3,H,W], radii[P] int32, geomBuffer, binningBuffer, imgBuffer, invdepth[1,H,W])."""
     if means3D.ndim != 2 or means3D.size(1) != 3:
@@ -166,21 +229,23 @@ def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_m
         color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
-        scratch = _Scratch(dev)
+        scratch = _Scratch(dev, lease)
         n = C.c_int(0)
         rc = lib().gsr_forward(C.byref(view), scratch.cbs[0], None, scratch.cbs[1], None, scratch.cbs[2], None,
                                color.data_ptr(), _ptr(radii), _ptr(invdepth), C.byref(n),
                                torch.cuda.current_stream(dev).cuda_stream)
-        if scratch.err is not None:
-            raise scratch.err
+        err = scratch.err
+        geom, binning, image = scratch.close()
+        if err is not None:
+            raise err
         _check(rc, "gsr_forward")
-    return n.value, color, radii, scratch.get("geom"), scratch.get("binning"), scratch.get("image"), invdepth
+    return n.value, color, radii, geom, binning, image, invdepth
 
 
 def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
                                  degree, campos, geomBuffer, R, binningBuffer, imageBuffer, antialiasing, debug,
-                                 want_conic=False, grad_sinks=None):
+                                 want_conic=False, grad_sinks=None, lease=None):
     """rasterize_points.cu:117-196. Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
     dL_dscales, dL_drotations); gradients of inputs that were not supplied are None. With want_conic=True a 9th
     tensor dL_dconic[P,2,2] is appended (parity tests).
@@ -225,7 +290,8 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
                        _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot), _ptr(dL_dconic), 0 if grad_sinks is None else 1)
             dpix = _f32(dL_dout_color)
             dinv = _f32(dL_dout_invdepth) if dL_dout_invdepth is not None else None
-            acc = torch.empty(int(lib().gsr_backward_scratch_bytes(P)), dtype=torch.uint8, device=dev)
+            nacc = int(lib().gsr_backward_scratch_bytes(P))
+            acc = lease.take(dev, nacc) if lease is not None else torch.empty(nacc, dtype=torch.uint8, device=dev)
             rc = lib().gsr_backward(C.byref(view), int(R), _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
                                     _ptr(imageBuffer), dpix.data_ptr(), _ptr(dinv), acc.data_ptr(), C.byref(g),
                                     torch.cuda.current_stream(dev).cuda_stream)

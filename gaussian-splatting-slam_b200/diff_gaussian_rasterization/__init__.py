@@ -44,11 +44,12 @@ class _RasterizeGaussians(torch.autograd.Function):
                 raster_settings, grad_sinks=None):
         rs = raster_settings
         antialiasing = bool(getattr(rs, "antialiasing", False))
+        lease = _C.ScratchLease()                    # scratch blobs go back to the pool when this context dies
         args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
-                rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, antialiasing)
+                rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, antialiasing, True, lease)
         if rs.debug:
-            cpu_args = cpu_deep_copy_tuple(args)     # snapshot before anything can be corrupted
+            cpu_args = cpu_deep_copy_tuple(args[:-2])    # snapshot before anything can be corrupted
             try:
                 res = _C.rasterize_gaussians(*args)
             except Exception as ex:
@@ -63,6 +64,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.antialiasing = antialiasing
         ctx.num_rendered = num_rendered
         ctx.grad_sinks = grad_sinks
+        ctx.scratch_lease = lease
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
                               geomBuffer, binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
@@ -80,9 +82,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         args = (rs.bg, means3D, radii, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, grad_out_invdepth, sh,
                 rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, ctx.antialiasing,
-                rs.debug, False, ctx.grad_sinks)
+                rs.debug, False, ctx.grad_sinks, ctx.scratch_lease)
         if rs.debug:
-            cpu_args = cpu_deep_copy_tuple(args)
+            cpu_args = cpu_deep_copy_tuple(args[:-3])
             try:
                 res = _C.rasterize_gaussians_backward(*args)
             except Exception as ex:
