@@ -266,4 +266,9 @@ int gsr_debug_sorted_keys(const gsr_view* view, int R, const char* geom, const c
     return launch_sorted_keys_debug(*view, g, b, R, keys_out, (cudaStream_t)stream);
 }
 
+int gsr_debug_exp_mismatches(unsigned long long* mismatches_dev, void* stream) {
+    if (!mismatches_dev) return GSR_E_BADARG;
+    return launch_exp_check(mismatches_dev, (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -48,6 +48,8 @@ def lib():
         L.gsr_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.gsr_dist2.restype = C.c_int
         L.gsr_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.gsr_debug_exp_mismatches.restype = C.c_int
+        L.gsr_debug_exp_mismatches.argtypes = [C.c_void_p, C.c_void_p]
         L.gsr_debug_sorted_keys.restype = C.c_int
         L.gsr_debug_sorted_keys.argtypes = [C.POINTER(_View), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         for n in ("gsr_required_geom", "gsr_required_image", "gsr_backward_scratch_bytes", "gsr_dist2_temp_bytes"):
@@ -382,3 +384,13 @@ def sorted_keys(P, R, geomBuffer, binningBuffer):
                                                keys.data_ptr(), torch.cuda.current_stream(dev).cuda_stream),
                    "gsr_debug_sorted_keys")
     return keys
+
+
+def exp_mismatches(device="cuda"):
+    """Parity helper: how many of the 2^32 float bit patterns the blend kernels' packed exp gets differently from expf."""
+    dev = torch.device(device)
+    n = torch.zeros(1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _check(lib().gsr_debug_exp_mismatches(n.data_ptr(), torch.cuda.current_stream(dev).cuda_stream),
+               "gsr_debug_exp_mismatches")
+    return int(n.item())

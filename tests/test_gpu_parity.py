@@ -281,6 +281,12 @@ def test_empty_and_all_culled():
     assert all(np.abs(v).max() == 0 for v in ours["grads"].values())
 
 
+def test_packed_exp_is_bit_identical_to_expf_for_every_float():
+    """The blend kernels' two-value exp (FFMA2 restatement of CUDA expf) vs expf over all 2^32 bit patterns."""
+    from diff_gaussian_rasterization import _C
+    assert _C.exp_mismatches(DEV) == 0
+
+
 def test_mark_visible_and_validation_errors():
     from diff_gaussian_rasterization import GaussianRasterizer
     sc, cam = scenes.make_c1(P=4000), scenes.c1_camera()
