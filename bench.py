@@ -186,8 +186,6 @@ class OursArm:
         # pinned staging for the end-to-end leg
         self.cam_pinned = [torch.cat([c.viewmatrix.reshape(-1), c.projmatrix.reshape(-1), c.campos.reshape(-1)]).pin_memory()
                            for c in cams]
-        self.cam_dev_buf = torch.empty(35, device=dev)
-        self.dpix_dev_buf = torch.empty_like(self.dpix)
         self.color_host = torch.empty(3, args.height, args.width).pin_memory()
         self.last = None
 
@@ -214,16 +212,59 @@ class OursArm:
         self.bucket.all_reduce()
 
     def step_e2e(self):
-        """Same step, host buffers: camera + dL/dpixel H2D from pinned memory, rendered image D2H, every view."""
+        """Same step, host buffers: every view's camera + dL/dpixel come from pinned host memory and its rendered image goes
+        back to pinned host memory. The copies ride two side streams and double buffers, so view i+1's upload and view
+        i-1's download overlap view i's kernels; the step ends when all three streams have drained."""
+        torch = self.torch
+        if not hasattr(self, "_e2e"):
+            n = 2
+            self._e2e = dict(
+                h2d=torch.cuda.Stream(self.dev), d2h=torch.cuda.Stream(self.dev),
+                cam=[torch.empty(35, device=self.dev) for _ in range(n)],
+                dpix=[torch.empty_like(self.dpix) for _ in range(n)],
+                host=[torch.empty(3, self.args.height, self.args.width).pin_memory() for _ in range(n)],
+                up=[torch.cuda.Event() for _ in range(n)], used=[torch.cuda.Event() for _ in range(n)],
+                down=[torch.cuda.Event() for _ in range(n)])
+        e = self._e2e
+        main = torch.cuda.current_stream(self.dev)
         self.bucket.zero()
         self.bucket.attach()
         self.means2D.grad = None
-        for cam, pinned in zip(self.cams_host, self.cam_pinned):
-            self.cam_dev_buf.copy_(pinned, non_blocking=True)
-            self.dpix_dev_buf.copy_(self.dpix_host, non_blocking=True)
-            b = self.cam_dev_buf
-            color = self._view(self._settings(cam, b[0:16].view(4, 4), b[16:32].view(4, 4), b[32:35]), self.dpix_dev_buf)
-            self.color_host.copy_(color.detach(), non_blocking=True)
+        n_views = len(self.cams_host)
+
+        def upload(i):
+            k = i % 2
+            with torch.cuda.stream(e["h2d"]):
+                if i >= 2:
+                    e["h2d"].wait_event(e["used"][k])            # view i-2 is done with this buffer pair
+                e["cam"][k].copy_(self.cam_pinned[i], non_blocking=True)
+                e["dpix"][k].copy_(self.dpix_host, non_blocking=True)
+                e["up"][k].record(e["h2d"])
+
+        upload(0)
+        for i, cam in enumerate(self.cams_host):
+            k = i % 2
+            if i + 1 < n_views:
+                upload(i + 1)
+            main.wait_event(e["up"][k])
+            b = e["cam"][k]
+            p = self.params
+            color, radii, _invd = self.Rasterizer(self._settings(cam, b[0:16].view(4, 4), b[16:32].view(4, 4), b[32:35]))(
+                means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"], shs=p["shs"], scales=p["scales"],
+                rotations=p["rotations"], grad_sinks=None if self.args.no_grad_sinks else self.bucket.views)
+            rendered = torch.cuda.Event()
+            rendered.record(main)
+            with torch.cuda.stream(e["d2h"]):                     # the image goes home while the backward runs
+                e["d2h"].wait_event(rendered)
+                if i >= 2:
+                    e["d2h"].wait_event(e["down"][k])
+                e["host"][k].copy_(color.detach(), non_blocking=True)
+                e["down"][k].record(e["d2h"])
+                color.record_stream(e["d2h"])
+            torch.autograd.backward([color], [e["dpix"][k]])
+            e["used"][k].record(main)
+            self.last = (color, radii)
+        main.wait_stream(e["d2h"])
         self.bucket.all_reduce()
 
     def state_of_view(self, i):
