@@ -275,7 +275,9 @@ class OursArm:
         R, _color, radii, geom, binning, img, _ = self._C.rasterize_gaussians(
             self.bg, p["means3D"], e, p["opacities"], p["scales"], p["rotations"], 1.0, e, v, pj, cam.tanfovx, cam.tanfovy,
             cam.H, cam.W, p["shs"], self.deg, cp, False, False, False)
-        return R, radii, self._C.decode_state(self.args.gaussians, R, cam.W, cam.H, geom, binning, img)
+        st = self._C.decode_state(self.args.gaussians, R, cam.W, cam.H, geom, binning, img)
+        st["pair_counts"] = self._C.blend_stats(self.args.gaussians, R, cam.W, cam.H, geom, binning, img)
+        return R, radii, st
 
     def e2e_bytes(self):
         n = len(self.cams_host)
@@ -327,7 +329,8 @@ def work_model(arm, args):
     P = args.gaussians
     R, radii, st = arm.state_of_view(len(arm.cams_host) - 1)
     visible = int((radii > 0).sum())
-    traversed = int(st["n_contrib"].to(torch.int64).sum())
+    traversed, contributing = st["pair_counts"]          # what renderCUDA iterates / what passes its alpha test
+    assert traversed == int(st["n_contrib"].to(torch.int64).sum())
     tiles = ((args.width + 15) // 16) * ((args.height + 15) // 16)
     N = args.width * args.height
     sort_tiles_P, sort_tiles_R = (P + 4095) // 4096, (R + 4095) // 4096
@@ -344,14 +347,15 @@ def work_model(arm, args):
         "scan_apply": ("hbm", 12.0 * P),
         "emit_instances": ("hbm", 8.0 * P + 28.0 * visible + 8.0 * R),
         "tile_ranges": ("hbm", 4.0 * R + 8.0 * tiles),
-        # 13 flop for every (pixel, list entry) pair up to the pixel's last contributor (power + alpha test); the 9
-        # further flop of a contributing pair are not counted (lower bound)
-        "blend_forward": ("fp32", 13.0 * traversed),
-        "blend_backward": ("fp32", 13.0 * traversed),
+        # 13 flop for every (pixel, list entry) pair the reference iterates (power + alpha test);
+        # a contributing pair costs 22 flop in the forward and ~80 in the backward
+        "blend_forward": ("fp32", 13.0 * (traversed - contributing) + 22.0 * contributing),
+        "blend_backward": ("fp32", 13.0 * (traversed - contributing) + 80.0 * contributing),
         "memset_grad_acc": ("hbm", 48.0 * P),
         "preprocess_bwd": ("hbm", 563.0 * visible + (4.0 + 236.0) * (P - visible)),
     }
-    return w, dict(num_rendered=R, visible=visible, traversed_pairs=traversed, mean_list_len=R / tiles, pixels=N)
+    return w, dict(num_rendered=R, visible=visible, traversed_pairs=traversed, contributing_pairs=contributing,
+                   mean_list_len=R / tiles, pixels=N)
 
 
 def kernel_table(report, views):

@@ -266,6 +266,20 @@ int gsr_debug_sorted_keys(const gsr_view* view, int R, const char* geom, const c
     return launch_sorted_keys_debug(*view, g, b, R, keys_out, (cudaStream_t)stream);
 }
 
+int gsr_debug_blend_stats(const gsr_view* view, int R, const char* geom, const char* binning, const char* image,
+                          unsigned long long* counts_dev, void* stream) {
+    if (!view || view->W <= 0 || view->H <= 0 || !geom || !image || !counts_dev) return GSR_E_BADARG;
+    if (R <= 0 || view->P <= 0) return 0;
+    if (!binning) return GSR_E_BADARG;
+    char* gp = const_cast<char*>(geom);
+    char* bp = const_cast<char*>(binning);
+    char* ip = const_cast<char*>(image);
+    GeomState g = GeomState::from(gp, (size_t)view->P);
+    BinningState b = BinningState::from(bp, (size_t)R);
+    ImageState img = ImageState::from(ip, (size_t)view->W * view->H, (size_t)tiles_of(view->W, view->H));
+    return launch_blend_stats(*view, g, b, img, counts_dev, (cudaStream_t)stream);
+}
+
 int gsr_debug_exp_mismatches(unsigned long long* mismatches_dev, void* stream) {
     if (!mismatches_dev) return GSR_E_BADARG;
     return launch_exp_check(mismatches_dev, (cudaStream_t)stream);

@@ -148,6 +148,8 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
 static inline int radix_passes(int total_bits) { return (total_bits + 7) / 8; }
 int launch_sorted_keys_debug(const gsr_view& v, const GeomState& g, const BinningState& b, int R, uint64_t* keys_out,
                              cudaStream_t s);
+int launch_blend_stats(const gsr_view& v, const GeomState& g, const BinningState& b, const ImageState& img,
+                       unsigned long long* out, cudaStream_t s);
 int launch_exp_check(unsigned long long* mismatches_dev, cudaStream_t s);
 int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s);
 size_t dist2_temp_bytes(int P);

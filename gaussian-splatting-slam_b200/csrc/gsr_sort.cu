@@ -201,7 +201,7 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t* __re
 }
 
 template <int BITS>
-__global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_t* __restrict__ keys_in,
+__global__ void __launch_bounds__(kSortThreads, 4) onesweep_kernel(const uint32_t* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     uint32_t* __restrict__ keys_out,
                                                                     uint32_t* __restrict__ vals_out, int n, int shift,

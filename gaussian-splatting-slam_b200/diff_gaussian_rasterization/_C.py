@@ -48,6 +48,8 @@ def lib():
         L.gsr_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.gsr_dist2.restype = C.c_int
         L.gsr_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.gsr_debug_blend_stats.restype = C.c_int
+        L.gsr_debug_blend_stats.argtypes = [C.POINTER(_View), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.gsr_debug_exp_mismatches.restype = C.c_int
         L.gsr_debug_exp_mismatches.argtypes = [C.c_void_p, C.c_void_p]
         L.gsr_debug_sorted_keys.restype = C.c_int
@@ -394,3 +396,18 @@ def exp_mismatches(device="cuda"):
         _check(lib().gsr_debug_exp_mismatches(n.data_ptr(), torch.cuda.current_stream(dev).cuda_stream),
                "gsr_debug_exp_mismatches")
     return int(n.item())
+
+
+def blend_stats(P, R, W, H, geomBuffer, binningBuffer, imgBuffer):
+    """Work counters of a forward: (pairs up to each pixel's last contributor, contributing pairs)."""
+    dev = geomBuffer.device
+    n = torch.zeros(2, dtype=torch.int64, device=dev)
+    if R > 0:
+        view = _View()
+        view.P, view.W, view.H = P, W, H
+        with torch.cuda.device(dev):
+            _check(lib().gsr_debug_blend_stats(C.byref(view), R, geomBuffer.data_ptr(), binningBuffer.data_ptr(),
+                                               imgBuffer.data_ptr(), n.data_ptr(),
+                                               torch.cuda.current_stream(dev).cuda_stream), "gsr_debug_blend_stats")
+    t = n.tolist()
+    return int(t[0]), int(t[1])
