@@ -1,0 +1,79 @@
+"""Turn the ncu captures in gpurun_out/ into the tracked summaries under profiles/ (run here, no GPU needed).
+
+  launches csv  -> profiles/<tag>_ncu_launches_bench.csv (copy) + per-kernel share table (json)
+  full .ncu-rep -> profiles/<tag>_ncu_full_summary.json (per kernel: duration, DRAM bytes, issue/pipe utilisation,
+                   occupancy, top stall reasons) and profiles/ncu_traffic.json (DRAM bytes per launch, read by bench.py)
+usage: summarize_profiles.py <tag> <launches.csv> <full.ncu-rep>
+"""
+import csv, json, os, re, shutil, subprocess, sys
+from collections import defaultdict
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+tag, launches, rep = sys.argv[1:4]
+out_dir = os.path.join(ROOT, "profiles")
+
+def short(name):
+    m = re.search(r"(\w+)_kernel", name)
+    if m:
+        return m.group(1)
+    return re.sub(r"\(.*", "", name).split("::")[-1][:40]
+
+# ---- launch list: share of the captured window per kernel
+rows = [r for r in csv.reader(open(launches)) if len(r) > 14 and r[0].isdigit()]
+tot = defaultdict(lambda: [0, 0.0])
+for r in rows:
+    k = short(r[4]); tot[k][0] += 1; tot[k][1] += float(r[14]) / 1e6
+total_ms = sum(v[1] for v in tot.values())
+share = {k: {"launches": v[0], "ms": round(v[1], 4), "share": round(v[1] / total_ms, 4)} for k, v in
+         sorted(tot.items(), key=lambda kv: -kv[1][1])}
+shutil.copy(launches, os.path.join(out_dir, f"{tag}_ncu_launches_bench.csv"))
+json.dump({"command": "ncu --metrics gpu__time_duration.sum --clock-control none -s 700 -c 300 python bench.py --steps 2 --warmup 3 "
+                      "--no-cpu-baseline --no-e2e", "captured_launches": len(rows), "total_ms": round(total_ms, 4),
+           "per_kernel": share}, open(os.path.join(out_dir, f"{tag}_ncu_launch_shares.json"), "w"), indent=1)
+
+# ---- full capture
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+r = list(csv.reader(raw.splitlines()))
+h, units, data = r[0], r[1], r[2:]
+col = {k: i for i, k in enumerate(h)}
+want = {"duration_us": "gpu__time_duration.sum", "dram_read_bytes": "dram__bytes_read.sum", "dram_write_bytes": "dram__bytes_write.sum",
+        "dram_pct_of_peak": "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "issue_active_pct": "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "warps_active_pct": "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "pipe_fma_pct": "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+        "pipe_alu_pct": "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
+        "warp_instructions": "smsp__inst_executed.sum", "registers": "launch__registers_per_thread",
+        "global_red_instr": "smsp__inst_executed_op_global_red.sum"}
+scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1, "ms": 1e3, "us": 1, "ns": 1e-3, "s": 1e6}
+summary, traffic = {}, defaultdict(list)
+for row in data:
+    k = short(row[col["Kernel Name"]])
+    if "Kernel Name" not in col:
+        break
+    tmpl = re.search(r"<\(?(?:bool\)|int\))?(\w+)>", row[col["Kernel Name"]])
+    e = {}
+    for name, metric in want.items():
+        if metric in col and row[col[metric]] not in ("", "n/a"):
+            v = float(row[col[metric]].replace(",", ""))
+            u = units[col[metric]]
+            e[name] = round(v * scale.get(u, 1), 3) if name.endswith("bytes") or name == "duration_us" else round(v, 3)
+    stalls = {}
+    for i, c in enumerate(h):
+        if c.startswith("smsp__average_warps_issue_stalled_") and c.endswith("_per_issue_active.ratio") and "not_issued" not in c:
+            try:
+                stalls[c[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")]] = round(float(row[i]), 2)
+            except ValueError:
+                pass
+    e["stalls_per_issue"] = dict(sorted(stalls.items(), key=lambda kv: -kv[1])[:5])
+    e["grid"] = row[col["Grid Size"]] if "Grid Size" in col else None
+    summary.setdefault(k, []).append(e)
+    traffic[k].append(e.get("dram_read_bytes", 0) + e.get("dram_write_bytes", 0))
+json.dump({"command": "ncu --set full --clock-control none --import-source on python tools/prof_view.py 2  (one 3M-Gaussian 1080p view)",
+           "kernels": summary}, open(os.path.join(out_dir, f"{tag}_ncu_full_summary.json"), "w"), indent=1)
+# bench.py names (per-launch DRAM bytes, mean over the captured launches of that kernel)
+name_map = {"blend_forward": "blend_forward", "blend_backward": "blend_backward", "preprocess_fwd": "preprocess_fwd",
+            "preprocess_bwd": "preprocess_bwd", "emit_instances": "emit_instances", "onesweep": "onesweep_pass",
+            "radix_hist": "radix_hist", "tile_ranges": "tile_ranges"}
+tr = {name_map[k]: round(sum(v) / len(v)) for k, v in traffic.items() if k in name_map}
+json.dump(tr, open(os.path.join(out_dir, "ncu_traffic.json"), "w"), indent=1)
+print(json.dumps(share, indent=1)); print(json.dumps(tr))
