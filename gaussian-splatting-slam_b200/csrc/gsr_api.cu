@@ -266,6 +266,32 @@ int gsr_debug_sorted_keys(const gsr_view* view, int R, const char* geom, const c
     return launch_sorted_keys_debug(*view, g, b, R, keys_out, (cudaStream_t)stream);
 }
 
+int gsr_ssim_forward(int B, int CH, int H, int W, float C1, float C2, const float* img1, const float* img2,
+                     float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12, double* sums, void* stream) {
+    if (B < 0 || CH < 0 || H <= 0 || W <= 0) return GSR_E_BADARG;
+    const bool train = dm_dmu1 != nullptr;
+    if ((dm_dsigma1_sq != nullptr) != train || (dm_dsigma12 != nullptr) != train) return GSR_E_BADARG;
+    if ((long long)B * CH > 65535) return GSR_E_TOOLARGE;
+    if (B * CH == 0) return 0;
+    if (!img1 || !img2 || (!ssim_map && !sums && !train)) return GSR_E_BADARG;
+    (void)C1; (void)C2;
+    return launch_ssim_forward(B * CH, H, W, C1, C2, img1, img2, ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, sums,
+                               (cudaStream_t)stream);
+}
+
+int gsr_ssim_backward(int B, int CH, int H, int W, float C1, float C2, const float* img1, const float* img2,
+                      const float* dL_dmap, float map_scale, float l1_scale, const float* upstream,
+                      const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimg1,
+                      void* stream) {
+    (void)C1; (void)C2;   // the derivative maps already carry them (ssim.cu:272-366 takes them and never reads them)
+    if (B < 0 || CH < 0 || H <= 0 || W <= 0) return GSR_E_BADARG;
+    if ((long long)B * CH > 65535) return GSR_E_TOOLARGE;
+    if (B * CH == 0) return 0;
+    if (!img1 || !img2 || !dm_dmu1 || !dm_dsigma1_sq || !dm_dsigma12 || !dL_dimg1) return GSR_E_BADARG;
+    return launch_ssim_backward(B * CH, H, W, img1, img2, dL_dmap, map_scale, l1_scale, upstream, dm_dmu1, dm_dsigma1_sq, dm_dsigma12,
+                                dL_dimg1, (cudaStream_t)stream);
+}
+
 int gsr_debug_blend_stats(const gsr_view* view, int R, const char* geom, const char* binning, const char* image,
                           unsigned long long* counts_dev, void* stream) {
     if (!view || view->W <= 0 || view->H <= 0 || !geom || !image || !counts_dev) return GSR_E_BADARG;

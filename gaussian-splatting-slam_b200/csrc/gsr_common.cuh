@@ -150,6 +150,11 @@ int launch_sorted_keys_debug(const gsr_view& v, const GeomState& g, const Binnin
                              cudaStream_t s);
 int launch_blend_stats(const gsr_view& v, const GeomState& g, const BinningState& b, const ImageState& img,
                        unsigned long long* out, cudaStream_t s);
+int launch_ssim_forward(int planes, int H, int W, float C1, float C2, const float* img1, const float* img2, float* ssim_map,
+                        float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12, double* sums, cudaStream_t s);
+int launch_ssim_backward(int planes, int H, int W, const float* img1, const float* img2, const float* dL_dmap,
+                         float map_scale, float l1_scale, const float* upstream, const float* dm_dmu1,
+                         const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimg1, cudaStream_t s);
 int launch_exp_check(unsigned long long* mismatches_dev, cudaStream_t s);
 int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s);
 size_t dist2_temp_bytes(int P);

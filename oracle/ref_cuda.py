@@ -133,3 +133,12 @@ def autograd_function():
             return (g["dL_dmeans3D"], g["dL_dmeans2D"], g["dL_dsh"], g["dL_dopacity"], g["dL_dscales"],
                     g["dL_drotations"], None)
     return _RefRasterize
+
+
+def ssim_available():
+    return os.path.exists(os.path.join(_REF, "ref_fused_ssim_cuda.so"))
+
+
+def fused_ssim_cuda():
+    """The UNMODIFIED reference fused-ssim extension (ssim.cu + ext.cpp): fusedssim / fusedssim_backward."""
+    return _load("ref_fused_ssim_cuda")
