@@ -292,6 +292,18 @@ int gsr_ssim_backward(int B, int CH, int H, int W, float C1, float C2, const flo
                                 dL_dimg1, (cudaStream_t)stream);
 }
 
+int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, double beta2, double eps, const uint8_t* visible,
+                  void* stream) {
+    if (n_groups < 0 || n_groups > GSR_ADAM_MAX_GROUPS || (n_groups > 0 && !groups)) return GSR_E_BADARG;
+    for (int k = 0; k < n_groups; k++) {
+        const gsr_adam_group& g = groups[k];
+        if (g.numel < 0 || g.row_len <= 0) return GSR_E_BADARG;
+        if (g.numel > 0 && (!g.param || !g.grad || !g.exp_avg || !g.exp_avg_sq)) return GSR_E_BADARG;
+        if (g.numel > (1ll << 40)) return GSR_E_TOOLARGE;
+    }
+    return launch_adam(groups, n_groups, beta1, beta2, eps, visible, (cudaStream_t)stream);
+}
+
 int gsr_debug_blend_stats(const gsr_view* view, int R, const char* geom, const char* binning, const char* image,
                           unsigned long long* counts_dev, void* stream) {
     if (!view || view->W <= 0 || view->H <= 0 || !geom || !image || !counts_dev) return GSR_E_BADARG;

@@ -155,6 +155,7 @@ int launch_ssim_forward(int planes, int H, int W, float C1, float C2, const floa
 int launch_ssim_backward(int planes, int H, int W, const float* img1, const float* img2, const float* dL_dmap,
                          float map_scale, float l1_scale, const float* upstream, const float* dm_dmu1,
                          const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimg1, cudaStream_t s);
+int launch_adam(const gsr_adam_group* groups, int n, double b1, double b2, double eps, const uint8_t* visible, cudaStream_t s);
 int launch_exp_check(unsigned long long* mismatches_dev, cudaStream_t s);
 int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s);
 size_t dist2_temp_bytes(int P);
