@@ -51,6 +51,9 @@ def parse_args():
     ap.add_argument("--gaussians", type=int, default=3_000_000)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--workload", default="raster", choices=["raster", "train"],
+                    help="raster: rasterizer forward+backward (BASELINE metric); train: + fused L1/SSIM loss per view and one "
+                         "Adam step per step (BASELINE config 3, 'full train-step')")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
@@ -165,6 +168,14 @@ def device_params(sc, dev):
     return {n: getattr(sc, n).to(dev).contiguous().requires_grad_(True) for n in names}
 
 
+# The train-step workload runs the optimiser with the reference's groups (gaussian_model.py:160-167; shs = f_dc and
+# f_rest together here) but learning rate 0: Adam reads and writes every parameter and both moments exactly as in
+# training (same kernel, same bytes), while the synthetic scene -- and with it num_rendered and every list length --
+# stays the same from the first warm-up step to the last timed one. (With the real rates and a random target image
+# the scene drifts and consecutive steps time different workloads.)
+TRAIN_LRS = {"means3D": 0.0, "shs": 0.0, "opacities": 0.0, "scales": 0.0, "rotations": 0.0}
+
+
 class OursArm:
     name = "ours"
 
@@ -188,6 +199,14 @@ class OursArm:
                            for c in cams]
         self.color_host = torch.empty(3, args.height, args.width).pin_memory()
         self.last = None
+        self.train = args.workload == "train"
+        if self.train:
+            from fused_ssim import fused_l1_ssim_loss
+            import gsr_optim
+            self.loss_fn = fused_l1_ssim_loss
+            self.gt = torch.rand(3, args.height, args.width, generator=torch.Generator().manual_seed(7)).to(dev)
+            self.opt = gsr_optim.FusedAdam([{"params": [self.params[k]], "lr": lr, "name": k} for k, lr in TRAIN_LRS.items()],
+                                           lr=0.0, eps=1e-15)
 
     def _settings(self, cam, view, proj, campos):
         return self.Settings(image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=self.bg,
@@ -199,7 +218,10 @@ class OursArm:
         color, radii, _invd = self.Rasterizer(st)(means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"],
                                                   shs=p["shs"], scales=p["scales"], rotations=p["rotations"],
                                                   grad_sinks=None if self.args.no_grad_sinks else self.bucket.views)
-        self.torch.autograd.backward([color], [dpix])
+        if self.train:
+            self.loss_fn(color, self.gt, 0.2).backward()          # train.py:114-122 (lambda_dssim = 0.2)
+        else:
+            self.torch.autograd.backward([color], [dpix])
         self.last = (color, radii)
         return color
 
@@ -210,6 +232,8 @@ class OursArm:
         for cam, (v, pj, cp) in zip(self.cams_host, self.cams_dev):
             self._view(self._settings(cam, v, pj, cp), self.dpix)
         self.bucket.all_reduce()
+        if self.train:
+            self.opt.step()
 
     def step_e2e(self):
         """Same step, host buffers: every view's camera + dL/dpixel come from pinned host memory and its rendered image goes
@@ -261,11 +285,16 @@ class OursArm:
                 e["host"][k].copy_(color.detach(), non_blocking=True)
                 e["down"][k].record(e["d2h"])
                 color.record_stream(e["d2h"])
-            torch.autograd.backward([color], [e["dpix"][k]])
+            if self.train:
+                self.loss_fn(color, self.gt, 0.2).backward()
+            else:
+                torch.autograd.backward([color], [e["dpix"][k]])
             e["used"][k].record(main)
             self.last = (color, radii)
         main.wait_stream(e["d2h"])
         self.bucket.all_reduce()
+        if self.train:
+            self.opt.step()
 
     def state_of_view(self, i):
         """Forward of view i through the binding (outside any timed region) and its decoded scratch state."""
@@ -305,6 +334,12 @@ class ReferenceArm:
         self.cams_dev = [(c.viewmatrix.to(dev), c.projmatrix.to(dev), c.campos.to(dev)) for c in cams]
         self.dpix = dpix_host.to(dev)
         self.fn = ref_cuda.autograd_function()
+        self.train = args.workload == "train"
+        if self.train:
+            self.ssim = ref_cuda.fused_ssim_function()               # the reference's fused-ssim CUDA build
+            self.gt = torch.rand(3, args.height, args.width, generator=torch.Generator().manual_seed(7)).to(dev)
+            self.opt = torch.optim.Adam([{"params": [self.params[k]], "lr": lr, "name": k} for k, lr in TRAIN_LRS.items()],
+                                        lr=0.0, eps=1e-15)          # scene/gaussian_model.py:168
 
     def step(self):
         self.bucket.zero()
@@ -315,7 +350,14 @@ class ReferenceArm:
             color, _radii = self.fn.apply(p["means3D"], self.means2D, p["shs"], p["opacities"], p["scales"], p["rotations"],
                                           dict(bg=self.bg, viewmatrix=v, projmatrix=pj, campos=cp, tanfovx=cam.tanfovx,
                                                tanfovy=cam.tanfovy, H=cam.H, W=cam.W, sh_degree=self.deg))
-            self.torch.autograd.backward([color], [self.dpix])
+            if self.train:                                           # train.py:114-122
+                l1 = self.torch.abs(color - self.gt).mean()
+                loss = 0.8 * l1 + 0.2 * (1.0 - self.ssim(color.unsqueeze(0), self.gt.unsqueeze(0)))
+                loss.backward()
+            else:
+                self.torch.autograd.backward([color], [self.dpix])
+        if self.train:
+            self.opt.step()
 
     def launches(self):
         return 0
@@ -352,6 +394,10 @@ def work_model(arm, args):
         "blend_forward": ("fp32", 13.0 * (traversed - contributing) + 22.0 * contributing),
         "blend_backward": ("fp32", 13.0 * (traversed - contributing) + 80.0 * contributing),
         "memset_grad_acc": ("hbm", 48.0 * P),
+        # fused loss: read both images, write the three derivative maps / read them + both images, write dL/dimage
+        "ssim_forward": ("hbm", 20.0 * 3 * N), "ssim_backward": ("hbm", 24.0 * 3 * N),
+        # p, g, m, v read + p, m, v written, 59 floats per Gaussian; one launch per STEP (reported per view)
+        "adam_step": ("hbm", 28.0 * 59 * P / args.views_per_step),
         "preprocess_bwd": ("hbm", 563.0 * visible + (4.0 + 236.0) * (P - visible)),
     }
     return w, dict(num_rendered=R, visible=visible, traversed_pairs=traversed, contributing_pairs=contributing,
@@ -586,7 +632,9 @@ def _main(out_fd):
                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                "fwd_bwd_ms_per_iter": round(ms_per_step / args.views_per_step, 4),
                "config": {"workload": f"C3: {args.gaussians} Gaussians SH3 (Mip-NeRF360-scale mixture, seed 2), "
-                                      f"{args.width}x{args.height}, orbit cameras; rasterizer forward+backward",
+                                      f"{args.width}x{args.height}, orbit cameras; rasterizer forward+backward" +
+                                      ("" if args.workload == "raster" else
+                                       " + fused L1/SSIM loss per view + one Adam step over all parameters per step (full train-step)"),
                           "views_per_step_per_gpu": args.views_per_step, "global_views_per_step": args.views_per_step * ref_world,
                           "parallelism": f"view-parallel dp{ref_world}, replicated Gaussians" +
                                          (", NCCL all-reduce of 59 floats/Gaussian per step" if ref_world > 1 else ""),

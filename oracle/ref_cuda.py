@@ -142,3 +142,23 @@ def ssim_available():
 def fused_ssim_cuda():
     """The UNMODIFIED reference fused-ssim extension (ssim.cu + ext.cpp): fusedssim / fusedssim_backward."""
     return _load("ref_fused_ssim_cuda")
+
+
+def fused_ssim_function():
+    """mean-SSIM callable over the reference extension, shaped like the reference's fused_ssim/__init__.py:8-41 (harness)."""
+    ext = fused_ssim_cuda()
+
+    class _Map(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, C1, C2, img1, img2):
+            m, d1, d2, d3 = ext.fusedssim(C1, C2, img1, img2, True)
+            ctx.save_for_backward(img1.detach(), img2, d1, d2, d3)
+            ctx.C1, ctx.C2 = C1, C2
+            return m
+
+        @staticmethod
+        def backward(ctx, g):
+            img1, img2, d1, d2, d3 = ctx.saved_tensors
+            return None, None, ext.fusedssim_backward(ctx.C1, ctx.C2, img1, img2, g.contiguous(), d1, d2, d3), None
+
+    return lambda a, b: _Map.apply(0.01 ** 2, 0.03 ** 2, a, b).mean()
