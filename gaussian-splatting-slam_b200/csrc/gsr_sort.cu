@@ -108,30 +108,60 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const uint32_t
 }
 
 // ------------------------------------------------------------------ one pass
+// Persistent CTAs (3 per SM): a CTA draws tile tickets in a loop and cp.async-prefetches the NEXT tile's pairs into
+// shared memory while it ranks / reorders / writes the current one, so global loads are in flight all the time
+// (a single-tile-per-CTA version spent half its cycles waiting for its own loads: 1.5 TB/s).
 struct SortSmem {
+    uint32_t pf_keys[GSR_SORT_TILE];         // prefetched pairs of the tile about to be processed (cp.async)
+    uint32_t pf_vals[GSR_SORT_TILE];
+    uint32_t s_keys[GSR_SORT_TILE];          // reorder buffers
+    uint32_t s_vals[GSR_SORT_TILE];
     uint32_t whist[kSortWarps][GSR_RADIX];   // per-warp digit counters, then local start of (warp, digit)
     uint32_t gofs[GSR_RADIX];                // global start of the digit's run minus its local start
-    uint32_t s_keys[GSR_SORT_TILE];
-    uint32_t s_vals[GSR_SORT_TILE];
     uint32_t warp_sums[kSortWarps];
-    uint32_t tile;
+    uint32_t tile, next;
 };
 
+__device__ __forceinline__ void sort_cp16(void* smem, const void* gmem) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void sort_cp4(void* smem, const void* gmem) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(gmem) : "memory");
+}
+// all threads: start copying tile `tile` into the prefetch buffers (no wait)
+__device__ __forceinline__ void sort_prefetch(SortSmem& sm, const uint32_t* __restrict__ keys_in,
+                                              const uint32_t* __restrict__ vals_in, int n, int tile) {
+    const int t = threadIdx.x, base = tile * GSR_SORT_TILE;
+    if (base + GSR_SORT_TILE <= n) {                      // tile bases are 16 KB apart: 16-byte aligned
+#pragma unroll
+        for (int i = 0; i < GSR_SORT_TILE / 4 / kSortThreads; i++) {
+            const int q = (i * kSortThreads + t) * 4;
+            sort_cp16(&sm.pf_keys[q], keys_in + base + q);
+            sort_cp16(&sm.pf_vals[q], vals_in + base + q);
+        }
+    } else {
+        for (int q = t; base + q < n; q += kSortThreads) {
+            sort_cp4(&sm.pf_keys[q], keys_in + base + q);
+            sort_cp4(&sm.pf_vals[q], vals_in + base + q);
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+// ranks, publishes, reorders and writes out one tile whose pairs are already in registers
 template <int BITS, bool FULL>
-__device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t* __restrict__ keys_in,
-                                              const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ keys_out,
-                                              uint32_t* __restrict__ vals_out, int n, int shift, int tile, uint32_t gbase,
-                                              uint32_t* __restrict__ status) {
+__device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key)[kSortItems], const uint32_t (&val)[kSortItems],
+                                              uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n,
+                                              int shift, int tile, uint32_t gbase, uint32_t* __restrict__ status) {
     constexpr uint32_t mask = (1u << BITS) - 1u;
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     const int base = tile * GSR_SORT_TILE;
     const int count = FULL ? GSR_SORT_TILE : n - base;
-    // warp-striped load: order index inside the tile = w*512 + i*32 + lane
-    uint32_t key[kSortItems], rank[kSortItems];
+    // order index inside the tile = w*512 + i*32 + lane (warp-striped)
+    uint32_t rank[kSortItems];
     const int wofs = w * (32 * kSortItems) + lane;
-    const uint32_t* kp = keys_in + base + wofs;
-#pragma unroll
-    for (int i = 0; i < kSortItems; i++) key[i] = (FULL || wofs + i * 32 < count) ? __ldg(kp + i * 32) : 0xFFFFFFFFu;
     const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
@@ -156,11 +186,6 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t* __re
 #pragma unroll
     for (int k = 0; k < kSortWarps; k++) { sm.whist[k][t] = acc; acc += cnt[k]; }
     __syncthreads();
-    // values are only needed now: load them late so they do not occupy registers during the ranking
-    uint32_t val[kSortItems];
-    const uint32_t* vp = vals_in + base + wofs;
-#pragma unroll
-    for (int i = 0; i < kSortItems; i++) val[i] = (FULL || wofs + i * 32 < count) ? __ldg(vp + i * 32) : 0u;
     // reorder inside shared memory
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
@@ -170,18 +195,29 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t* __re
             sm.s_vals[lp] = val[i];
         }
     }
-    // decoupled look-back for digit t
+    // decoupled look-back for digit t, kLookWin predecessors per round trip: the status words of a window are loaded
+    // together (independent L2 reads in flight) and then consumed in order; a serial walk paid one L2 latency per
+    // predecessor and was a third of the pass
     uint32_t excl = 0;
     if (tile > 0) {
-        for (int j = tile - 1;; --j) {
-            const uint32_t* ps = status + (size_t)j * GSR_RADIX + t;
-            uint32_t s = ld_relaxed(ps);
-            while ((s >> 30) == 0u) {
-                __nanosleep(32);
-                s = ld_relaxed(ps);
+        constexpr int kLookWin = 8;
+        bool done = false;
+        for (int j = tile - 1; !done; j -= kLookWin) {
+            uint32_t sw[kLookWin];
+#pragma unroll
+            for (int q = 0; q < kLookWin; q++)
+                sw[q] = (j - q >= 0) ? ld_relaxed(status + (size_t)(j - q) * GSR_RADIX + t) : kFlagInc;   // before tile 0: inclusive 0
+#pragma unroll
+            for (int q = 0; q < kLookWin; q++) {
+                if (done) break;
+                uint32_t sv = sw[q];
+                while ((sv >> 30) == 0u) {
+                    __nanosleep(32);
+                    sv = ld_relaxed(status + (size_t)(j - q) * GSR_RADIX + t);
+                }
+                excl += sv & kValMask;
+                done = (sv >> 30) == 2u;
             }
-            excl += s & kValMask;
-            if ((s >> 30) == 2u) break;
         }
         st_relaxed(my_status, kFlagInc | (excl + run));
     }
@@ -201,30 +237,56 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t* __re
 }
 
 template <int BITS>
-__global__ void __launch_bounds__(kSortThreads, 4) onesweep_kernel(const uint32_t* __restrict__ keys_in,
+__global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_t* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     uint32_t* __restrict__ keys_out,
-                                                                    uint32_t* __restrict__ vals_out, int n, int shift,
-                                                                    const uint32_t* __restrict__ ghist,
+                                                                    uint32_t* __restrict__ vals_out, int n, int n_tiles,
+                                                                    int shift, const uint32_t* __restrict__ ghist,
                                                                     uint32_t* __restrict__ ticket,
                                                                     uint32_t* __restrict__ status) {
-    __shared__ SortSmem sm;
-    const int t = threadIdx.x;
+    extern __shared__ __align__(16) unsigned char sort_smem_raw[];
+    SortSmem& sm = *reinterpret_cast<SortSmem*>(sort_smem_raw);
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     if (t == 0) sm.tile = atomicAdd(ticket, 1u);
-#pragma unroll
-    for (int k = 0; k < kSortWarps; k++) sm.whist[k][t] = 0;
     const uint32_t gbase = block_excl_scan256(__ldg(ghist + t), sm.warp_sums);   // first output slot of digit t (syncs)
-    const int tile = (int)sm.tile;
-    if ((tile + 1) * GSR_SORT_TILE <= n)
-        onesweep_tile<BITS, true>(sm, keys_in, vals_in, keys_out, vals_out, n, shift, tile, gbase, status);
-    else
-        onesweep_tile<BITS, false>(sm, keys_in, vals_in, keys_out, vals_out, n, shift, tile, gbase, status);
+    int tile = (int)sm.tile;
+    if (tile >= n_tiles) return;
+    sort_prefetch(sm, keys_in, vals_in, n, tile);
+    const int wofs = w * (32 * kSortItems) + lane;
+    while (true) {
+        if (t == 0) sm.next = atomicAdd(ticket, 1u);
+#pragma unroll
+        for (int k = 0; k < kSortWarps; k++) sm.whist[k][t] = 0;
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();                                   // the tile's pairs, the next ticket and the cleared counters are visible
+        const int next = (int)sm.next;
+        uint32_t key[kSortItems], val[kSortItems];
+#pragma unroll
+        for (int i = 0; i < kSortItems; i++) { key[i] = sm.pf_keys[wofs + i * 32]; val[i] = sm.pf_vals[wofs + i * 32]; }
+        __syncthreads();                                   // everybody holds its pairs: the prefetch buffers are free again
+        if (next < n_tiles) sort_prefetch(sm, keys_in, vals_in, n, next);
+        if ((tile + 1) * GSR_SORT_TILE <= n)
+            onesweep_tile<BITS, true>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
+        else
+            onesweep_tile<BITS, false>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
+        if (next >= n_tiles) break;
+        tile = next;
+        __syncthreads();                                   // reorder buffers / gofs are read until here
+    }
 }
 
 template <int BITS>
-static void launch_pass(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, int n, int shift,
-                        const uint32_t* ghist, uint32_t* ticket, uint32_t* status, int tiles, cudaStream_t s) {
-    onesweep_kernel<BITS><<<tiles, kSortThreads, 0, s>>>(kin, vin, kout, vout, n, shift, ghist, ticket, status);
+static int launch_pass(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, int n, int shift,
+                       const uint32_t* ghist, uint32_t* ticket, uint32_t* status, int tiles, cudaStream_t s) {
+    static bool attr_set = false;                          // one process drives one device
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(onesweep_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    const int ctas = tiles < 148 * 3 ? tiles : 148 * 3;
+    onesweep_kernel<BITS><<<ctas, kSortThreads, sizeof(SortSmem), s>>>(kin, vin, kout, vout, n, tiles, shift, ghist, ticket, status);
+    return 0;
 }
 
 int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits, uint32_t* scratch,
@@ -246,18 +308,20 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
         const int bits = (total_bits - shift) < 8 ? (total_bits - shift) : 8;
         uint32_t* st = status + (size_t)p * tiles * GSR_RADIX;
         const uint32_t* gh = ghist + p * GSR_RADIX;
+        int le = 0;
         GSR_LAUNCH("onesweep_pass", debug, s, {
             switch (bits) {
-                case 1: launch_pass<1>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 2: launch_pass<2>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 3: launch_pass<3>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 4: launch_pass<4>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 5: launch_pass<5>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 6: launch_pass<6>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 7: launch_pass<7>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                default: launch_pass<8>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 1: le = launch_pass<1>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 2: le = launch_pass<2>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 3: le = launch_pass<3>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 4: le = launch_pass<4>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 5: le = launch_pass<5>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 6: le = launch_pass<6>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                case 7: le = launch_pass<7>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
+                default: le = launch_pass<8>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
             }
         });
+        if (le) return le;
         uint32_t* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
     }
