@@ -293,7 +293,7 @@ struct PreBwdArgs {
 };
 
 template <bool SH16>
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdArgs b) {
+__global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs b) {
     const PreArgs& a = b.f;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P) return;
