@@ -67,8 +67,10 @@ static bool view_ok(const gsr_view* v) {
     if (!v || v->P < 0 || v->W <= 0 || v->H <= 0) return false;
     if (v->P == 0) return true;
     if (!v->means3D || !v->opacities || !v->viewmatrix || !v->projmatrix || !v->background) return false;
-    if (!v->shs && !v->colors_precomp) return false;
-    if (v->shs && (!v->cam_pos || v->M < (v->D + 1) * (v->D + 1) || v->D < 0 || v->D > 3)) return false;
+    const bool has_sh = v->shs || v->sh_dc;
+    if (!has_sh && !v->colors_precomp) return false;
+    if (has_sh && (!v->cam_pos || v->M < (v->D + 1) * (v->D + 1) || v->D < 0 || v->D > 3)) return false;
+    if (v->sh_dc && v->M > 1 && !v->shs) return false;      /* dc given: the M-1 higher coefficients must come too */
     if (!v->cov3D_precomp && (!v->scales || !v->rotations)) return false;
     return true;
 }
@@ -216,6 +218,7 @@ int gsr_backward(const gsr_view* view, int R, const int* radii, const char* geom
         !out->dL_dmeans3D || (R > 0 && !binning))
         return GSR_E_BADARG;
     if (v.shs && !out->dL_dsh) return GSR_E_BADARG;
+    if (v.sh_dc && !out->dL_ddc) return GSR_E_BADARG;
     cudaStream_t s = (cudaStream_t)stream;
     char* gp = const_cast<char*>(geom);
     char* ip = const_cast<char*>(image);
@@ -237,6 +240,7 @@ int gsr_backward(const gsr_view* view, int R, const int* radii, const char* geom
     }
     gsr_grads o = *out;
     if (!v.shs) o.dL_dsh = nullptr;
+    if (!v.sh_dc) o.dL_ddc = nullptr;
     if (!v.scales) { o.dL_dscales = nullptr; o.dL_drotations = nullptr; }
     return launch_preprocess_backward(v, g, radii, acc, dL_dinvdepth != nullptr, o, s);
 }

@@ -111,9 +111,20 @@ __device__ __forceinline__ float3 cov2d_of(const float3& mean, float focal_x, fl
     return {cov.c[0][0], cov.c[0][1], cov.c[1][1]};
 }
 
+// Coefficient k of Gaussian idx lives at sh_ptr(...)[0..2]: in the fused layout all M coefficients are contiguous; with
+// a separate degree-0 tensor (gsr_view::sh_dc) coefficient 0 comes from there and shs holds the other M-1.
+__device__ __forceinline__ const float* sh_ptr(const float* shs, const float* dc, int idx, int M, int k) {
+    if (dc == nullptr) return shs + ((size_t)idx * M + k) * 3;
+    return k == 0 ? dc + (size_t)idx * 3 : shs + ((size_t)idx * (M - 1) + (k - 1)) * 3;
+}
+__device__ __forceinline__ float* sh_ptr(float* shs, float* dc, int idx, int M, int k) {
+    if (dc == nullptr) return shs + ((size_t)idx * M + k) * 3;
+    return k == 0 ? dc + (size_t)idx * 3 : shs + ((size_t)idx * (M - 1) + (k - 1)) * 3;
+}
+
 template <bool SH16>
 __device__ __forceinline__ V3 sh_color(int idx, int deg, int max_coeffs, V3 pos, V3 campos, const float* shs,
-                                       uint8_t& clamp_bits) {
+                                       const float* dc, uint8_t& clamp_bits) {
     V3 dir = pos - campos;
     dir = dir / sqrtf(dot3(dir, dir));
     V3 sh[16];
@@ -131,10 +142,13 @@ __device__ __forceinline__ V3 sh_color(int idx, int deg, int max_coeffs, V3 pos,
 #pragma unroll
         for (int k = 0; k < 16; k++) sh[k] = {f[3 * k], f[3 * k + 1], f[3 * k + 2]};
     } else {
-        const float* p = shs + (size_t)idx * max_coeffs * 3;
 #pragma unroll
-        for (int k = 0; k < 16; k++)
-            sh[k] = (k < nb) ? V3{__ldg(p + 3 * k), __ldg(p + 3 * k + 1), __ldg(p + 3 * k + 2)} : V3{0.f, 0.f, 0.f};
+        for (int k = 0; k < 16; k++) {
+            if (k < nb) {
+                const float* p = sh_ptr(shs, dc, idx, max_coeffs, k);
+                sh[k] = V3{__ldg(p), __ldg(p + 1), __ldg(p + 2)};
+            } else sh[k] = V3{0.f, 0.f, 0.f};
+        }
     }
     V3 result = kC0 * sh[0];
     if (deg > 0) {
@@ -163,7 +177,7 @@ struct PreArgs {
     int P, D, M, W, H;
     float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
     int prefiltered, antialiasing;
-    const float *means3D, *shs, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
+    const float *means3D, *shs, *sh_dc, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
     const float *view, *proj, *campos;   // device pointers (16, 16, 3 floats)
 };
 
@@ -220,9 +234,9 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreArgs a, in
 
         V3 color;
         uint8_t cb = 0;
-        if (a.colors_precomp == nullptr) {
+        if (a.colors_precomp == nullptr) {      // SH input (fused, or dc + rest)
             color = sh_color<SH16>(idx, a.D, a.M, V3{p_orig.x, p_orig.y, p_orig.z},
-                                   V3{__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2)}, a.shs, cb);
+                                   V3{__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2)}, a.shs, a.sh_dc, cb);
         } else {
             color = {__ldg(a.colors_precomp + 3 * idx), __ldg(a.colors_precomp + 3 * idx + 1),
                      __ldg(a.colors_precomp + 3 * idx + 2)};
@@ -271,7 +285,7 @@ static void fill_pre_args(const gsr_view& v, PreArgs& a) {
     a.focal_y = v.H / (2.0f * v.tan_fovy);             // rasterizer_impl.cu:221-222
     a.focal_x = v.W / (2.0f * v.tan_fovx);
     a.scale_modifier = v.scale_modifier; a.prefiltered = v.prefiltered; a.antialiasing = v.antialiasing;
-    a.means3D = v.means3D; a.shs = v.shs; a.colors_precomp = v.colors_precomp; a.opacities = v.opacities;
+    a.means3D = v.means3D; a.shs = v.shs; a.sh_dc = v.sh_dc; a.colors_precomp = v.colors_precomp; a.opacities = v.opacities;
     a.scales = v.scales; a.rotations = v.rotations; a.cov3D_precomp = v.cov3D_precomp;
     a.view = v.viewmatrix; a.proj = v.projmatrix; a.campos = v.cam_pos;
 }
@@ -417,7 +431,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
         dmean[1] += (proj[4] * m_w - proj[7] * mul1) * dmean2d[0] + (proj[5] * m_w - proj[7] * mul2) * dmean2d[1];
         dmean[2] += (proj[8] * m_w - proj[11] * mul1) * dmean2d[0] + (proj[9] * m_w - proj[11] * mul2) * dmean2d[1];
         // ---- SH backward (backward.cu:20-139)
-        if (a.shs != nullptr) {
+        if (a.shs != nullptr || a.sh_dc != nullptr) {
             const uint8_t cbits = b.clamped[idx];
             dRGB[0] = (cbits & 1) ? 0.f : dcolor[0];
             dRGB[1] = (cbits & 2) ? 0.f : dcolor[1];
@@ -443,10 +457,13 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
 #pragma unroll
                 for (int k = 0; k < 16; k++) sd[k] = f[3 * k] * dRGB[0] + f[3 * k + 1] * dRGB[1] + f[3 * k + 2] * dRGB[2];
             } else {
-                const float* p = a.shs + (size_t)idx * M * 3;
 #pragma unroll
-                for (int k = 0; k < 16; k++)
-                    sd[k] = (k < nb) ? (__ldg(p + 3 * k) * dRGB[0] + __ldg(p + 3 * k + 1) * dRGB[1] + __ldg(p + 3 * k + 2) * dRGB[2]) : 0.f;
+                for (int k = 0; k < 16; k++) {
+                    if (k < nb) {
+                        const float* p = sh_ptr(a.shs, a.sh_dc, idx, M, k);
+                        sd[k] = __ldg(p) * dRGB[0] + __ldg(p + 1) * dRGB[1] + __ldg(p + 2) * dRGB[2];
+                    } else sd[k] = 0.f;
+                }
             }
             float ddx = 0.f, ddy = 0.f, ddz = 0.f;   // dL/ddir
             sh_coef[0] = kC0;
@@ -544,7 +561,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
         for (int k = 0; k < 3; k++) put(o.dL_dscales + 3 * (size_t)idx + k, dscale[k]);
     }
     if (o.dL_drotations) put4(reinterpret_cast<float4*>(o.dL_drotations) + idx, make_float4(drot[0], drot[1], drot[2], drot[3]));
-    if (o.dL_dsh) {
+    if (o.dL_dsh || o.dL_ddc) {
         if (SH16) {
             float f[48];
 #pragma unroll
@@ -558,10 +575,12 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
             for (int k = 0; k < 12; k++)
                 if (k < nq) put4(dst + k, make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]));
         } else {
-            float* dst = o.dL_dsh + (size_t)idx * M * 3;
-            for (int k = 0; k < M; k++) {
+            // accumulate mode: coefficients above the active degree have zero gradient and need no traffic
+            const int kmax = accum ? min(M, (a.D + 1) * (a.D + 1)) : M;
+            for (int k = 0; k < kmax; k++) {
                 const float c = k < 16 ? sh_coef[k < 16 ? k : 0] : 0.f;
-                put(dst + 3 * k, c * dRGB[0]); put(dst + 3 * k + 1, c * dRGB[1]); put(dst + 3 * k + 2, c * dRGB[2]);
+                float* dst = sh_ptr(o.dL_dsh, o.dL_ddc, idx, M, k);
+                put(dst, c * dRGB[0]); put(dst + 1, c * dRGB[1]); put(dst + 2, c * dRGB[2]);
             }
         }
     }
@@ -569,7 +588,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
 
 // ---------------------------------------------------------------------------------------------
 static bool sh16_fast(const gsr_view& v) {
-    return v.shs != nullptr && v.M == 16 && (reinterpret_cast<uintptr_t>(v.shs) & 15) == 0;
+    return v.sh_dc == nullptr && v.shs != nullptr && v.M == 16 && (reinterpret_cast<uintptr_t>(v.shs) & 15) == 0;
 }
 
 int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s) {

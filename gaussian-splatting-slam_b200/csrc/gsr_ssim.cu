@@ -21,7 +21,8 @@ namespace gsr {
 constexpr int kST = 32;                 // tile edge (outputs)
 constexpr int kSH = 5;                  // halo
 constexpr int kSP = kST + 2 * kSH;      // staged edge: 42
-constexpr int kSPad = 44;               // row stride of the staged tiles
+constexpr int kSPad = 45;               // row stride of the staged tiles (odd: lanes walking down a column hit 32 banks)
+constexpr int kHPad = kST + 1;          // row stride of the horizontally filtered planes (same reason)
 constexpr int kSsimThreads = 256;
 
 __constant__ float kG[11] = {0.001028380123898387f, 0.0075987582094967365f, 0.036000773310661316f, 0.10936068743467331f,
@@ -47,7 +48,7 @@ __global__ void __launch_bounds__(kSsimThreads) ssim_fwd_kernel(int H, int W, fl
                                                                  float* __restrict__ dm_dsigma1_sq,
                                                                  float* __restrict__ dm_dsigma12, double* __restrict__ sums) {
     __shared__ float a[kSP][kSPad], b[kSP][kSPad];
-    __shared__ float h[5][kSP][kST];
+    __shared__ float h[5][kSP][kHPad];
     __shared__ float red[8];
     const int tid = threadIdx.x;
     const size_t plane = (size_t)blockIdx.z * H * W;
@@ -60,9 +61,10 @@ __global__ void __launch_bounds__(kSsimThreads) ssim_fwd_kernel(int H, int W, fl
         b[ly][lx] = in ? __ldg(img2 + plane + (size_t)gy * W + gx) : 0.0f;
     }
     __syncthreads();
-    // horizontal: 42 rows x 8 segments of 4 outputs; 14-wide register window per image
+    // horizontal: 8 segments of 4 outputs x 42 rows (consecutive lanes = consecutive rows: conflict-free with the odd
+    // strides); 14-wide register window per image
     for (int item = tid; item < kSP * (kST / 4); item += kSsimThreads) {
-        const int row = item >> 3, c0 = (item & 7) * 4;
+        const int seg = item / kSP, row = item - seg * kSP, c0 = seg * 4;
         float va[14], vb[14];
 #pragma unroll
         for (int k = 0; k < 14; k++) { va[k] = a[row][c0 + k]; vb[k] = b[row][c0 + k]; }
@@ -142,7 +144,7 @@ __global__ void __launch_bounds__(kSsimThreads) ssim_bwd_kernel(int H, int W, co
                                                                  const float* __restrict__ dm_dsigma12,
                                                                  float* __restrict__ dL_dimg1) {
     __shared__ float p[3][kSP][kSPad];
-    __shared__ float h[3][kSP][kST];
+    __shared__ float h[3][kSP][kHPad];
     const int tid = threadIdx.x;
     const size_t plane = (size_t)blockIdx.z * H * W;
     const int x0 = blockIdx.x * kST, y0 = blockIdx.y * kST;
@@ -160,7 +162,7 @@ __global__ void __launch_bounds__(kSsimThreads) ssim_bwd_kernel(int H, int W, co
     }
     __syncthreads();
     for (int item = tid; item < kSP * (kST / 4); item += kSsimThreads) {
-        const int row = item >> 3, c0 = (item & 7) * 4;
+        const int seg = item / kSP, row = item - seg * kSP, c0 = seg * 4;
 #pragma unroll
         for (int s = 0; s < 3; s++) {
             float v[14];

@@ -18,12 +18,13 @@ class _View(C.Structure):
                 ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
                 ("prefiltered", C.c_int), ("antialiasing", C.c_int), ("debug", C.c_int)] + \
                [(n, C.c_void_p) for n in ("background", "means3D", "shs", "colors_precomp", "opacities", "scales",
-                                          "rotations", "cov3D_precomp", "viewmatrix", "projmatrix", "cam_pos")]
+                                          "rotations", "cov3D_precomp", "viewmatrix", "projmatrix", "cam_pos", "sh_dc")]
 
 
 class _Grads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("dL_dmeans2D", "dL_dopacity", "dL_dmeans3D", "dL_dcolors", "dL_dcov3D",
-                                          "dL_dsh", "dL_dscales", "dL_drotations", "dL_dconic")] + [("accumulate", C.c_int)]
+                                          "dL_dsh", "dL_dscales", "dL_drotations", "dL_dconic", "dL_ddc")] + \
+               [("accumulate", C.c_int)]
 
 
 _ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
@@ -196,11 +197,13 @@ class _Scratch:
 
 
 def _make_view(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
-               projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug, antialiasing, keep):
+               projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug, antialiasing, keep, dc=None):
     M = sh.size(1) if sh.numel() != 0 else 0          # rasterize_points.cu:84-88
+    if dc is not None and dc.numel() != 0:            # separate_sh: dc [P,1,3] + the M-1 higher coefficients in `sh`
+        M += 1
     ts = dict(background=bg, means3D=means3D, shs=sh, colors_precomp=colors, opacities=opacity, scales=scales,
               rotations=rotations, cov3D_precomp=cov3D_precomp, viewmatrix=viewmatrix, projmatrix=projmatrix,
-              cam_pos=campos)
+              cam_pos=campos, sh_dc=dc)
     ptrs = {}
     for k, t in ts.items():
         if t is None or t.numel() == 0:
@@ -213,13 +216,14 @@ def _make_view(bg, means3D, colors, opacity, scales, rotations, scale_modifier, 
                  float(scale_modifier), int(bool(prefiltered)), int(bool(antialiasing)), int(bool(debug)),
                  ptrs["background"], ptrs["means3D"], ptrs["shs"], ptrs["colors_precomp"], ptrs["opacities"],
                  ptrs["scales"], ptrs["rotations"], ptrs["cov3D_precomp"], ptrs["viewmatrix"], ptrs["projmatrix"],
-                 ptrs["cam_pos"])
+                 ptrs["cam_pos"], ptrs["sh_dc"])
 
 
 def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                         projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
-                        debug, antialiasing=False, want_invdepth=True, lease=None):
-    """rasterize_points.cu:35-115 + superset outputs. Returns
+                        debug, antialiasing=False, want_invdepth=True, lease=None, dc=None):
+    """rasterize_points.cu:35-115 + superset outputs (`dc`: the degree-0 SH coefficient as its own [P,1,3] tensor,
+    `sh` then holds the higher ones -- the caller's separate_sh call shape). Returns
     (num_rendered, color[3,H,W], radii[P] int32, geomBuffer, binningBuffer, imgBuffer, invdepth[1,H,W])."""
     if means3D.ndim != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")   # rasterize_points.cu:57-59
@@ -229,7 +233,8 @@ def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_m
     with torch.cuda.device(dev):
         keep = []
         view = _make_view(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
-                          projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug, antialiasing, keep)
+                          projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, prefiltered, debug, antialiasing, keep,
+                          dc=dc)
         color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
@@ -249,10 +254,11 @@ def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_m
 def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh,
                                  degree, campos, geomBuffer, R, binningBuffer, imageBuffer, antialiasing, debug,
-                                 want_conic=False, grad_sinks=None, lease=None):
+                                 want_conic=False, grad_sinks=None, lease=None, dc=None):
     """rasterize_points.cu:117-196. Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
     dL_dscales, dL_drotations); gradients of inputs that were not supplied are None. With want_conic=True a 9th
-    tensor dL_dconic[P,2,2] is appended (parity tests).
+    tensor dL_dconic[P,2,2] is appended (parity tests). With `dc` (separate_sh) one more tensor, dL_ddc[P,1,3], comes
+    last and dL_dsh covers the higher coefficients only (grad_sinks key: "dc").
     grad_sinks (superset, multi-view batches): dict of fp32 contiguous CUDA tensors keyed by input name ("means3D",
     "opacities", "shs" | "colors_precomp", "scales" + "rotations" | "cov3D_precomp"), one for EVERY supplied input. The
     gradients of this view are then ADDED into them inside the kernel (gsr_grads.accumulate) and the corresponding
@@ -263,14 +269,17 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
     with torch.cuda.device(dev):
         keep = []
         view = _make_view(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
-                          projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, False, debug, antialiasing, keep)
-        M = view.M
+                          projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, False, debug, antialiasing, keep,
+                          dc=dc)
+        has_dc = dc is not None and dc.numel() != 0
+        M = view.M - (1 if has_dc else 0)             # rows of `sh` / dL_dsh
         f = dict(dtype=torch.float32, device=dev)
         dL_dmeans2D = torch.empty((P, 3), **f)
         dL_dconic = torch.empty((P, 2, 2), **f) if want_conic else None
         shapes = dict(means3D=(P, 3), opacities=(P, 1), colors_precomp=(P, 3) if colors.numel() != 0 else None,
                       cov3D_precomp=(P, 6) if cov3D_precomp.numel() != 0 else None,
-                      shs=(P, M, 3) if sh.numel() != 0 else None, scales=(P, 3) if scales.numel() != 0 else None,
+                      shs=(P, M, 3) if sh.numel() != 0 else None, dc=(P, 1, 3) if has_dc else None,
+                      scales=(P, 3) if scales.numel() != 0 else None,
                       rotations=(P, 4) if rotations.numel() != 0 else None)
         if grad_sinks is None:
             o = {k: (torch.empty(shp, **f) if shp is not None else None) for k, shp in shapes.items()}
@@ -288,10 +297,11 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
                     raise RuntimeError(f"grad_sinks['{k}'] must be a contiguous fp32 tensor of {shp} on {dev}")
                 o[k] = t
         dL_dmeans3D, dL_dopacity, dL_dcolors, dL_dcov3D = o["means3D"], o["opacities"], o["colors_precomp"], o["cov3D_precomp"]
-        dL_dsh, dL_dscales, dL_drot = o["shs"], o["scales"], o["rotations"]
+        dL_dsh, dL_dscales, dL_drot, dL_ddc = o["shs"], o["scales"], o["rotations"], o["dc"]
         if P != 0:
             g = _Grads(_ptr(dL_dmeans2D), _ptr(dL_dopacity), _ptr(dL_dmeans3D), _ptr(dL_dcolors), _ptr(dL_dcov3D),
-                       _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot), _ptr(dL_dconic), 0 if grad_sinks is None else 1)
+                       _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot), _ptr(dL_dconic), _ptr(dL_ddc),
+                       0 if grad_sinks is None else 1)
             dpix = _f32(dL_dout_color)
             dinv = _f32(dL_dout_invdepth) if dL_dout_invdepth is not None else None
             nacc = int(lib().gsr_backward_scratch_bytes(P))
@@ -301,9 +311,11 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
                                     torch.cuda.current_stream(dev).cuda_stream)
             _check(rc, "gsr_backward")
     if grad_sinks is not None:
-        dL_dcolors = dL_dopacity = dL_dmeans3D = dL_dcov3D = dL_dsh = dL_dscales = dL_drot = None
+        dL_dcolors = dL_dopacity = dL_dmeans3D = dL_dcov3D = dL_dsh = dL_dscales = dL_drot = dL_ddc = None
     out = (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drot)
-    return out + (dL_dconic,) if want_conic else out
+    if want_conic:
+        out = out + (dL_dconic,)
+    return out + (dL_ddc,) if has_dc else out
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

@@ -89,7 +89,11 @@ def test_python_api_surface_matches_reference(gsr_lib):
     z = torch.zeros(3)
     s12 = dgr.GaussianRasterizationSettings(8, 8, 1.0, 1.0, z, 1.0, torch.eye(4), torch.eye(4), 0, z, False, False)
     assert s12.antialiasing is False
-    assert not hasattr(dgr, "SparseGaussianAdam")           # would flip callers to separate_sh (train.py:37-41)
+    # the caller probes for it (train.py:37-41) and then renders with dc= / shs= (separate_sh), which forward() takes
+    import gsr_optim
+    assert dgr.SparseGaussianAdam is gsr_optim.SparseGaussianAdam
+    import inspect
+    assert "dc" in inspect.signature(dgr.GaussianRasterizer.forward).parameters
     r = dgr.GaussianRasterizer(s12)
     m = torch.zeros(4, 3)
     with pytest.raises(Exception, match="excatly one of either SHs"):

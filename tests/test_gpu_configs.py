@@ -142,3 +142,49 @@ def test_config5_slam_incremental_map_aa_and_inverse_depth():
     ours = _run_ours(big, scenes.c5_camera(7), (0.0, 0.0, 0.0), antialiasing=True)
     _invariants(ours, 200_000)
     assert np.isfinite(ours["invdepth"]).all() and (ours["invdepth"] >= 0).all()
+
+
+def test_separate_sh_dc_rest_call_shape_equals_fused_features():
+    """separate_sh (gaussian_renderer/__init__.py:81-99): dc [P,1,3] + shs [P,15,3] read in place must give the same image
+    (bit-identical: same arithmetic, different addresses) and the same gradients as the concatenated [P,16,3] features."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    for deg, P, cam in ((3, 30_000, scenes.orbit_camera(640, 360, 65.0, 4.0, 20.0)),
+                        (1, 5_000, scenes.look_at_camera(200, 123, math.radians(70), (0.3, -0.2, -3.5))),
+                        (0, 5_000, scenes.c1_camera())):
+        sc = scenes.make_c2(P=P, deg=3)._replace(sh_degree=deg)
+        st = cuda_settings(cam, (0.1, 0.2, 0.3), deg, DEV)
+        dpix = torch.randn(3, cam.H, cam.W, device=DEV, generator=torch.Generator(device=DEV).manual_seed(deg))
+        base = {n: getattr(sc, n).to(DEV) for n in ("means3D", "opacities", "scales", "rotations")}
+
+        def run(split, sinks=False):
+            p = {n: t.clone().requires_grad_(True) for n, t in base.items()}
+            m2 = torch.zeros_like(p["means3D"], requires_grad=True)
+            if split:
+                dc = sc.shs[:, :1].contiguous().to(DEV).requires_grad_(True)
+                rest = sc.shs[:, 1:].contiguous().to(DEV).requires_grad_(True)
+                kw = dict(dc=dc, shs=rest)
+            else:
+                full = sc.shs.to(DEV).requires_grad_(True)
+                kw = dict(shs=full)
+            gs = None
+            if sinks:
+                gs = {"means3D": torch.zeros_like(p["means3D"]), "opacities": torch.zeros_like(p["opacities"]),
+                      "scales": torch.zeros_like(p["scales"]), "rotations": torch.zeros_like(p["rotations"]),
+                      "dc": torch.zeros(P, 1, 3, device=DEV), "shs": torch.zeros(P, 15, 3, device=DEV)}
+            color, radii, _ = GaussianRasterizer(st)(means3D=p["means3D"], means2D=m2, opacities=p["opacities"],
+                                                     scales=p["scales"], rotations=p["rotations"], grad_sinks=gs, **kw)
+            torch.autograd.backward([color], [dpix])
+            if sinks:
+                return color.detach(), gs["means3D"], torch.cat([gs["dc"], gs["shs"]], 1), gs["opacities"]
+            gsh = torch.cat([kw["dc"].grad, kw["shs"].grad], 1) if split else kw["shs"].grad
+            return color.detach(), p["means3D"].grad, gsh, p["opacities"].grad
+
+        c0, gm0, gsh0, go0 = run(False)
+        c1, gm1, gsh1, go1 = run(True)
+        c2, gm2, gsh2, go2 = run(True, sinks=True)
+        assert torch.equal(c0, c1) and torch.equal(c0, c2), f"deg {deg}: image differs between fused and split features"
+        for a, b, n in ((gm0, gm1, "means3D"), (gsh0, gsh1, "sh"), (go0, go1, "opacity"), (gm0, gm2, "means3D/sinks"),
+                        (gsh0, gsh2, "sh/sinks"), (go0, go2, "opacity/sinks")):
+            assert rel_l2(b.cpu().numpy(), a.cpu().numpy()) < GRAD_TOL, f"deg {deg} {n}"
+        nb = (deg + 1) ** 2
+        assert gsh1[:, nb:].abs().max().item() == 0.0 if nb < 16 else True      # above the active degree: zero (A13)
