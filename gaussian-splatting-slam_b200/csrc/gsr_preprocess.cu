@@ -182,7 +182,7 @@ struct PreArgs {
 };
 
 template <bool SH16>
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreArgs a, int* __restrict__ radii,
+__global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a, int* __restrict__ radii,
                                                               float* __restrict__ depths, float4* __restrict__ rec,
                                                               uint8_t* __restrict__ clamped,
                                                               uint32_t* __restrict__ tiles_touched,
