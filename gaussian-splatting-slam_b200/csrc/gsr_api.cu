@@ -308,6 +308,46 @@ int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, doub
     return launch_adam(groups, n_groups, beta1, beta2, eps, visible, (cudaStream_t)stream);
 }
 
+size_t gsr_densify_plan_bytes(int P) { return P < 0 ? 0 : densify_plan_bytes((size_t)P); }
+
+int gsr_densify_plan(int P, const float* opacity, const float* scaling, const float* grad_accum, const float* denom,
+                     const gsr_densify_rule* rule, void* plan, uint32_t* counts_out, void* stream) {
+    if (P < 0 || !rule || !plan) return GSR_E_BADARG;
+    if (P > 0 && (!opacity || !scaling || !grad_accum || !denom)) return GSR_E_BADARG;
+    if (!(rule->grad_threshold > 0.0f) || rule->n_split < 1) return GSR_E_BADARG;   // clones (zero gradient) must not split
+    if (P >= (1 << 29)) return GSR_E_TOOLARGE;
+    return launch_densify_plan(P, opacity, scaling, grad_accum, denom, *rule, plan, counts_out, (cudaStream_t)stream);
+}
+
+int gsr_prune_plan(int P, const uint8_t* prune_mask, void* plan, uint32_t* counts_out, void* stream) {
+    if (P < 0 || !plan || (P > 0 && !prune_mask)) return GSR_E_BADARG;
+    if (P >= (1 << 29)) return GSR_E_TOOLARGE;
+    return launch_prune_plan(P, prune_mask, plan, counts_out, (cudaStream_t)stream);
+}
+
+int gsr_densify_apply(int P, const void* plan, const gsr_densify_rule* rule, const gsr_densify_tensor* tensors, int n_tensors,
+                      const float* scaling, const float* rotation, const float* noise, void* stream) {
+    if (P < 0 || !plan || n_tensors < 0 || n_tensors > GSR_DENSIFY_MAX_TENSORS || (n_tensors > 0 && !tensors)) return GSR_E_BADARG;
+    for (int k = 0; k < n_tensors; k++) {
+        const gsr_densify_tensor& t = tensors[k];
+        if (t.row_len <= 0 || (P > 0 && (!t.src || !t.dst))) return GSR_E_BADARG;
+        const int have = (t.src_m != nullptr) + (t.dst_m != nullptr) + (t.src_v != nullptr) + (t.dst_v != nullptr);
+        if (have != 0 && have != 4) return GSR_E_BADARG;
+        if (t.role != GSR_DENSIFY_COPY && t.role != GSR_DENSIFY_XYZ && t.role != GSR_DENSIFY_SCALING) return GSR_E_BADARG;
+        if (t.role != GSR_DENSIFY_COPY && !rule) return GSR_E_BADARG;
+        if (t.role == GSR_DENSIFY_XYZ && (t.row_len != 3 || (P > 0 && (!scaling || !rotation)))) return GSR_E_BADARG;
+        if (t.role == GSR_DENSIFY_SCALING && t.row_len != 3) return GSR_E_BADARG;
+    }
+    return launch_densify_apply(P, plan, rule, tensors, n_tensors, scaling, rotation, noise, (cudaStream_t)stream);
+}
+
+int gsr_densify_stats(int P, const float* dL_dmean2D, const uint8_t* update_filter, const int* radii, float* grad_accum,
+                      float* denom, float* max_radii2D, void* stream) {
+    if (P < 0) return GSR_E_BADARG;
+    if (P > 0 && (!dL_dmean2D || !grad_accum || !denom || (!update_filter && !radii))) return GSR_E_BADARG;
+    return launch_densify_stats(P, dL_dmean2D, update_filter, radii, grad_accum, denom, max_radii2D, (cudaStream_t)stream);
+}
+
 int gsr_debug_blend_stats(const gsr_view* view, int R, const char* geom, const char* binning, const char* image,
                           unsigned long long* counts_dev, void* stream) {
     if (!view || view->W <= 0 || view->H <= 0 || !geom || !image || !counts_dev) return GSR_E_BADARG;

@@ -155,6 +155,14 @@ int launch_ssim_forward(int planes, int H, int W, float C1, float C2, const floa
 int launch_ssim_backward(int planes, int H, int W, const float* img1, const float* img2, const float* dL_dmap,
                          float map_scale, float l1_scale, const float* upstream, const float* dm_dmu1,
                          const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimg1, cudaStream_t s);
+size_t densify_plan_bytes(size_t P);
+int launch_densify_plan(int P, const float* opacity, const float* scaling, const float* grad_accum, const float* denom,
+                        const gsr_densify_rule& rule, void* blob, uint32_t* counts_out, cudaStream_t s);
+int launch_prune_plan(int P, const uint8_t* prune_mask, void* blob, uint32_t* counts_out, cudaStream_t s);
+int launch_densify_apply(int P, const void* blob, const gsr_densify_rule* rule, const gsr_densify_tensor* tensors, int n,
+                         const float* scaling, const float* rotation, const float* noise, cudaStream_t s);
+int launch_densify_stats(int P, const float* dL_dmean2D, const uint8_t* update_filter, const int* radii, float* grad_accum,
+                         float* denom, float* max_radii2D, cudaStream_t s);
 int launch_adam(const gsr_adam_group* groups, int n, double b1, double b2, double eps, const uint8_t* visible, cudaStream_t s);
 int launch_exp_check(unsigned long long* mismatches_dev, cudaStream_t s);
 int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s);
