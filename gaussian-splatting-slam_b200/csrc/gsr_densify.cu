@@ -172,7 +172,7 @@ struct DensifyTable {
     int n;
 };
 
-constexpr int kDenPerCta = kDenThreads * 8;
+constexpr int kDenPerCta = kDenThreads * 8;    // source elements per CTA of the apply kernel
 
 // One component of build_rotation(q) @ sample + xyz (gaussian_model.py:379-383, general_utils.py:78-99). Every
 // product and sum of the reference is its own torch kernel, hence individually rounded: no contraction here either.
@@ -195,49 +195,113 @@ __device__ __forceinline__ float split_position(int c, const float* __restrict__
     return __fadd_rn(dot, center);
 }
 
-__global__ void __launch_bounds__(kDenThreads) densify_apply_kernel(const __grid_constant__ DensifyTable tab, int P,
-                                                                    DensifyPlan plan, int n_split, float shrink_inv,
-                                                                    const float* __restrict__ scaling,
-                                                                    const float* __restrict__ rotation,
-                                                                    const float* __restrict__ noise) {
+// exp_avg / exp_avg_sq of every appended row are zero (cat_tensors_to_optimizer, :331-332): the appended rows are the
+// contiguous tail of the output. Persistent grid, float4 stores once aligned.
+__global__ void __launch_bounds__(kDenThreads) densify_zero_kernel(const __grid_constant__ DensifyTable tab, DensifyPlan plan,
+                                                                   int n_split) {
+    const long long first = plan.counts[0];
+    const long long rows = (long long)plan.counts[1] + (long long)n_split * plan.counts[3];
+    for (int k = 0; k < tab.n; k++) {
+        const gsr_densify_tensor& T = tab.t[k];
+        if (!T.dst_m) continue;
+        const long long n = rows * T.row_len;
+        for (int which = 0; which < 2; which++) {
+            float* p = (which ? T.dst_v : T.dst_m) + first * T.row_len;
+            const long long head = min(n, (long long)((16 - (reinterpret_cast<uintptr_t>(p) & 15)) & 15) / 4);
+            const long long vec = (n - head) / 4;
+            float4* p4 = reinterpret_cast<float4*>(p + head);
+            for (long long j = (long long)blockIdx.x * kDenThreads + threadIdx.x; j < vec; j += (long long)gridDim.x * kDenThreads)
+                p4[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (blockIdx.x == 0) {
+                for (long long j = threadIdx.x; j < head; j += kDenThreads) p[j] = 0.0f;
+                for (long long j = head + vec * 4 + threadIdx.x; j < n; j += kDenThreads) p[j] = 0.0f;
+            }
+        }
+    }
+}
+
+// One CTA moves kDenPerCta consecutive source elements of one tensor (and of its two moment tensors):
+//   A. every thread fetches two quads of consecutive elements of src / exp_avg / exp_avg_sq with 16-byte loads -- 96 bytes
+//      in flight per thread, unconditionally, so that nothing waits on the plan -- and parks them in shared memory; the
+//      destination records of the rows the chunk touches are fetched alongside (coalesced 16-byte loads);
+//   B. element j of the chunk is then handled by thread j mod 256, so that the stores of a warp are 32 consecutive
+//      words of the destination row(s).
+// Rows that go nowhere (pruned, or split parents) are read for nothing: a few per cent of the map in a training run.
+// Moments of NEW rows are not written here: they are the contiguous tail [kept originals, P_new) of dst_m / dst_v,
+// cleared by densify_zero_kernel.
+constexpr int kDenRows = kDenPerCta / 3 + 3;        // rows a chunk can touch when row_len >= 3; narrower tensors read the plan directly
+
+__global__ void __launch_bounds__(kDenThreads, 5) densify_apply_kernel(const __grid_constant__ DensifyTable tab, int P,
+                                                                       DensifyPlan plan, int n_split, float shrink_inv,
+                                                                       const float* __restrict__ scaling,
+                                                                       const float* __restrict__ rotation,
+                                                                       const float* __restrict__ noise) {
+    __shared__ int4 s_dest[kDenRows];
+    __shared__ __align__(16) float s_val[3][kDenPerCta];
     int ti = 0;
 #pragma unroll
     for (int k = 1; k < GSR_DENSIFY_MAX_TENSORS; k++)
         if (k < tab.n && blockIdx.x >= tab.block_begin[k]) ti = k;
     const gsr_densify_tensor& T = tab.t[ti];
-    const int w = T.row_len;
+    const uint32_t w = (uint32_t)T.row_len;
     const long long total = (long long)P * w;
-    const long long base = (long long)(blockIdx.x - tab.block_begin[ti]) * kDenPerCta;
-    const uint32_t n_sel = plan.counts[2], n_kept = plan.counts[3];
+    const long long e0 = (long long)(blockIdx.x - tab.block_begin[ti]) * kDenPerCta;
+    const int count = (int)min((long long)kDenPerCta, total - e0);
+    const int row0 = (int)(e0 / w);
+    const uint32_t col0 = (uint32_t)(e0 - (long long)row0 * w);
+    const uint32_t magic = w > 1 ? (uint32_t)((1ull << 32) / w + 1) : 0;      // x / w = umulhi(x, magic) while x * w < 2^32
+    auto row_of = [&](uint32_t x) { return w > 1 ? __umulhi(x, magic) : x; };
+    const bool staged = w >= 3;
     const bool moments = T.src_m != nullptr;
+    const bool vec_ok = ((reinterpret_cast<uintptr_t>(T.src) | reinterpret_cast<uintptr_t>(T.src_m) |
+                          reinterpret_cast<uintptr_t>(T.src_v)) & 15) == 0;
+#pragma unroll
+    for (int half = 0; half < kDenPerCta / (4 * kDenThreads); half++) {
+        const int j = 4 * (half * kDenThreads + threadIdx.x);
+        if (j >= count) break;
+        if (vec_ok && j + 3 < count) {
+            *reinterpret_cast<float4*>(&s_val[0][j]) = __ldg(reinterpret_cast<const float4*>(T.src + e0 + j));
+            if (moments) {
+                *reinterpret_cast<float4*>(&s_val[1][j]) = __ldg(reinterpret_cast<const float4*>(T.src_m + e0 + j));
+                *reinterpret_cast<float4*>(&s_val[2][j]) = __ldg(reinterpret_cast<const float4*>(T.src_v + e0 + j));
+            }
+        } else {
+            for (int k = j; k < min(j + 4, count); k++) {
+                s_val[0][k] = __ldg(T.src + e0 + k);
+                if (moments) { s_val[1][k] = __ldg(T.src_m + e0 + k); s_val[2][k] = __ldg(T.src_v + e0 + k); }
+            }
+        }
+    }
+    if (staged) {
+        const int n_rows = (int)row_of(col0 + (uint32_t)count - 1) + 1;
+        for (int r = threadIdx.x; r < n_rows; r += kDenThreads) s_dest[r] = __ldg(&plan.dest[row0 + r]);
+    }
+    const uint32_t n_sel = plan.counts[2], n_kept = plan.counts[3];
+    __syncthreads();
+
 #pragma unroll 2
     for (int it = 0; it < kDenPerCta / kDenThreads; it++) {
-        const long long e = base + (long long)it * kDenThreads + threadIdx.x;
-        if (e >= total) return;
-        const int i = (int)(e / w), c = (int)(e - (long long)i * w);
-        const int4 d = __ldg(&plan.dest[i]);
-        if (d.x < 0 && d.y < 0 && d.z < 0) continue;
-        const float val = __ldg(T.src + e);
+        const int j = it * kDenThreads + threadIdx.x;
+        if (j >= count) break;
+        const uint32_t r = row_of(col0 + j), c = col0 + j - r * w;
+        const int4 d = staged ? s_dest[r] : __ldg(&plan.dest[row0 + r]);
+        if ((d.x & d.y & d.z) < 0) continue;                              // all three negative: the row goes nowhere
+        const float val = s_val[0][j];
         if (d.x >= 0) {
             const long long o = (long long)d.x * w + c;
             T.dst[o] = val;
-            if (moments) { T.dst_m[o] = __ldg(T.src_m + e); T.dst_v[o] = __ldg(T.src_v + e); }
+            if (moments) { T.dst_m[o] = s_val[1][j]; T.dst_v[o] = s_val[2][j]; }
         }
-        if (d.y >= 0) {
-            const long long o = (long long)d.y * w + c;
-            T.dst[o] = val;
-            if (moments) { T.dst_m[o] = 0.0f; T.dst_v[o] = 0.0f; }
-        }
+        if (d.y >= 0) T.dst[(long long)d.y * w + c] = val;
         if (d.z >= 0) {
+            const int i = row0 + (int)r;
             float child = val;
             if (T.role == GSR_DENSIFY_SCALING) child = logf(__fmul_rn(expf(val), shrink_inv));
             for (int rep = 0; rep < n_split; rep++) {
                 if (T.role == GSR_DENSIFY_XYZ)
-                    child = split_position(c, rotation + 4ll * i, scaling + 3ll * i,
+                    child = split_position((int)c, rotation + 4ll * i, scaling + 3ll * i,
                                            noise + 3ll * ((long long)rep * n_sel + d.w), val);
-                const long long o = ((long long)d.z + (long long)rep * n_kept) * w + c;
-                T.dst[o] = child;
-                if (moments) { T.dst_m[o] = 0.0f; T.dst_v[o] = 0.0f; }
+                T.dst[((long long)d.z + (long long)rep * n_kept) * w + c] = child;
             }
         }
     }
@@ -310,6 +374,9 @@ int launch_densify_apply(int P, const void* blob, const gsr_densify_rule* rule, 
     }
     tab.block_begin[n] = blocks;
     if (blocks == 0) return 0;
+    // zero moments for every new row: rows [counts[0], P_new) of dst_m / dst_v. The row counts live on the device, so
+    // the clear is a kernel over the worst case rather than a sized memset.
+    GSR_LAUNCH("densify_zero_moments", false, s, (densify_zero_kernel<<<148 * 8, kDenThreads, 0, s>>>(tab, plan, rule ? rule->n_split : 0)));
     GSR_LAUNCH("densify_apply", false, s, (densify_apply_kernel<<<blocks, kDenThreads, 0, s>>>(
                    tab, P, plan, rule ? rule->n_split : 0, rule ? rule->split_shrink_inv : 1.0f, scaling, rotation, noise)));
     return 0;
