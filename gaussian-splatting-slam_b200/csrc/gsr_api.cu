@@ -359,7 +359,9 @@ int gsr_debug_blend_stats(const gsr_view* view, int R, const char* geom, const c
     GeomState g = GeomState::from(gp, (size_t)view->P);
     BinningState b = BinningState::from(bp, (size_t)R);
     ImageState img = ImageState::from(ip, (size_t)view->W * view->H, (size_t)tiles_of(view->W, view->H));
-    return launch_blend_stats(*view, g, b, img, counts_dev, (cudaStream_t)stream);
+    int e = launch_blend_stats(*view, g, b, img, counts_dev, (cudaStream_t)stream);
+    if (e) return e;
+    return launch_cull_stats(*view, g, b, img, counts_dev, (cudaStream_t)stream);
 }
 
 int gsr_debug_exp_mismatches(unsigned long long* mismatches_dev, void* stream) {

@@ -413,7 +413,7 @@ def exp_mismatches(device="cuda"):
 def blend_stats(P, R, W, H, geomBuffer, binningBuffer, imgBuffer):
     """Work counters of a forward: (pairs up to each pixel's last contributor, contributing pairs)."""
     dev = geomBuffer.device
-    n = torch.zeros(2, dtype=torch.int64, device=dev)
+    n = torch.zeros(6, dtype=torch.int64, device=dev)
     if R > 0:
         view = _View()
         view.P, view.W, view.H = P, W, H
@@ -422,4 +422,5 @@ def blend_stats(P, R, W, H, geomBuffer, binningBuffer, imgBuffer):
                                                imgBuffer.data_ptr(), n.data_ptr(),
                                                torch.cuda.current_stream(dev).cuda_stream), "gsr_debug_blend_stats")
     t = n.tolist()
+    blend_stats.last_cull = [int(x) for x in t[2:]]
     return int(t[0]), int(t[1])
