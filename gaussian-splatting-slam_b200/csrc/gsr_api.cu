@@ -364,6 +364,8 @@ int gsr_debug_blend_stats(const gsr_view* view, int R, const char* geom, const c
     return launch_cull_stats(*view, g, b, img, counts_dev, (cudaStream_t)stream);
 }
 
+int gsr_debug_set_exact_cull(int on) { return set_exact_cull(on); }
+
 int gsr_debug_exp_mismatches(unsigned long long* mismatches_dev, void* stream) {
     if (!mismatches_dev) return GSR_E_BADARG;
     return launch_exp_check(mismatches_dev, (cudaStream_t)stream);

@@ -163,6 +163,7 @@ int launch_densify_apply(int P, const void* blob, const gsr_densify_rule* rule, 
                          const float* scaling, const float* rotation, const float* noise, cudaStream_t s);
 int launch_densify_stats(int P, const float* dL_dmean2D, const uint8_t* update_filter, const int* radii, float* grad_accum,
                          float* denom, float* max_radii2D, cudaStream_t s);
+int set_exact_cull(int on);
 int launch_cull_stats(const gsr_view& v, const GeomState& g, const BinningState& b, const ImageState& img,
                       unsigned long long* out, cudaStream_t s);
 int launch_adam(const gsr_adam_group* groups, int n, double b1, double b2, double eps, const uint8_t* visible, cudaStream_t s);

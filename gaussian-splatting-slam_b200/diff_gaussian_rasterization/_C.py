@@ -410,6 +410,11 @@ def exp_mismatches(device="cuda"):
     return int(n.item())
 
 
+def set_exact_cull(on):
+    """Parity helper (gsr_debug_set_exact_cull): switch the blend kernels' exact sub-tile cull off / on."""
+    _check(lib().gsr_debug_set_exact_cull(1 if on else 0), "gsr_debug_set_exact_cull")
+
+
 def blend_stats(P, R, W, H, geomBuffer, binningBuffer, imgBuffer):
     """Work counters of a forward: (pairs up to each pixel's last contributor, contributing pairs)."""
     dev = geomBuffer.device
