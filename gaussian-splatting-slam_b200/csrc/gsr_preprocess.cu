@@ -297,6 +297,13 @@ static void fill_pre_args(const gsr_view& v, PreArgs& a) {
 // (the reference splits them only for code length, backward.cu:583-586). Reads the packed
 // accumulator written by the backward blend; writes every gradient output in full (zeros for
 // Gaussians with radii == 0) so no zero-fill pass is needed.
+constexpr int kShRow = 52;     // floats per staged SH row: 16-byte reads of 8 consecutive rows fall into distinct banks
+__device__ __forceinline__ void pre_cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void pre_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void pre_cp_async_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 struct PreBwdArgs {
     PreArgs f;
     const int* radii;
@@ -310,10 +317,43 @@ template <bool SH16>
 __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs b) {
     const PreArgs& a = b.f;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.P) return;
+    const bool inside = idx < a.P;
+    if (!SH16 && !inside) return;                     // the SH16 path has CTA-wide barriers: everybody stays
     const gsr_grads& o = b.out;
-    const bool vis = b.radii[idx] > 0;
+    const bool vis = inside && b.radii[idx] > 0;
     const int M = a.M;
+    // SH16 path: the coefficient rows of the CTA's visible Gaussians are fetched COOPERATIVELY -- consecutive threads take
+    // consecutive 16-byte pieces, so one warp-wide request covers 4 lines instead of the 32 a row-per-thread access
+    // touches (the L1 tag stage, one line per cycle, was this kernel's busiest unit) -- with cp.async into shared
+    // memory, where they wait while the covariance backward runs. The dL/dsh rows leave the same way.
+    extern __shared__ __align__(16) float s_rows[];   // [256][kShRow]
+    __shared__ uint8_t s_owner[256];                  // slot -> thread of the visible Gaussian
+    __shared__ int s_warp[8];
+    const int n_quads = ((a.D + 1) * (a.D + 1) * 3 + 3) / 4;      // 16-byte pieces of a row that hold active coefficients
+    int slot = 0, n_vis = 0;
+    if (SH16) {
+        const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+        const unsigned m = __ballot_sync(0xffffffffu, vis);
+        if (lane == 0) s_warp[w] = __popc(m);
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const int c = s_warp[q];
+            slot += q < w ? c : 0;
+            n_vis += c;
+        }
+        slot += __popc(m & ((1u << lane) - 1u));
+        if (vis) s_owner[slot] = (uint8_t)threadIdx.x;
+        __syncthreads();
+        const float* src0 = a.shs + (size_t)blockIdx.x * 256 * 48;
+        for (int f = threadIdx.x; f < n_vis * n_quads; f += 256) {
+            const int sl = f / n_quads, k = f - sl * n_quads;
+            pre_cp_async16(s_rows + sl * kShRow + 4 * k, src0 + (size_t)s_owner[sl] * 48 + 4 * k);
+        }
+        pre_cp_async_commit();
+    }
+    float4* const my_row = reinterpret_cast<float4*>(s_rows + slot * kShRow);
+    float3 mean = {0.f, 0.f, 0.f};
 
     float dmean[3] = {0.f, 0.f, 0.f}, dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float dmean2d[2] = {0.f, 0.f}, dopac = 0.f, dcolor[3] = {0.f, 0.f, 0.f}, dconic[3] = {0.f, 0.f, 0.f};
@@ -332,7 +372,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
         dcolor[0] = a1.z; dcolor[1] = a1.w; dcolor[2] = a2.x;
         const float dinvd = b.have_invdepth ? a2.y : 0.f;
 
-        const float3 mean = {__ldg(a.means3D + 3 * idx), __ldg(a.means3D + 3 * idx + 1), __ldg(a.means3D + 3 * idx + 2)};
+        mean = make_float3(__ldg(a.means3D + 3 * idx), __ldg(a.means3D + 3 * idx + 1), __ldg(a.means3D + 3 * idx + 2));
         const float* view = a.view;
         const float* proj = a.proj;
         float c3[6];
@@ -430,7 +470,40 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
         dmean[0] += (proj[0] * m_w - proj[3] * mul1) * dmean2d[0] + (proj[1] * m_w - proj[3] * mul2) * dmean2d[1];
         dmean[1] += (proj[4] * m_w - proj[7] * mul1) * dmean2d[0] + (proj[5] * m_w - proj[7] * mul2) * dmean2d[1];
         dmean[2] += (proj[8] * m_w - proj[11] * mul1) * dmean2d[0] + (proj[9] * m_w - proj[11] * mul2) * dmean2d[1];
-        // ---- SH backward (backward.cu:20-139)
+        // ---- cov3D -> scale / rotation (backward.cu:278-341)
+        if (a.scales != nullptr) {
+            const float r = q.x, x = q.y, y = q.z, z = q.w;
+            const float Rm[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+                                    {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+                                    {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+            const float s[3] = {a.scale_modifier * sc[0], a.scale_modifier * sc[1], a.scale_modifier * sc[2]};
+            const float dS[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
+                                    {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
+                                    {0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
+            float Mt[3][3];   // reference's dL_dMt[a][b] (glm indexing) after scaling by s_a
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+                float dMi[3];
+#pragma unroll
+                for (int j = 0; j < 3; j++)
+                    dMi[j] = 2.0f * ((s[i] * Rm[0][i]) * dS[0][j] + (s[i] * Rm[1][i]) * dS[1][j] + (s[i] * Rm[2][i]) * dS[2][j]);
+                dscale[i] = Rm[0][i] * dMi[0] + Rm[1][i] * dMi[1] + Rm[2][i] * dMi[2];
+#pragma unroll
+                for (int j = 0; j < 3; j++) Mt[i][j] = s[i] * dMi[j];
+            }
+            drot[0] = 2 * z * (Mt[0][1] - Mt[1][0]) + 2 * y * (Mt[2][0] - Mt[0][2]) + 2 * x * (Mt[1][2] - Mt[2][1]);
+            drot[1] = 2 * y * (Mt[1][0] + Mt[0][1]) + 2 * z * (Mt[2][0] + Mt[0][2]) + 2 * r * (Mt[1][2] - Mt[2][1]) - 4 * x * (Mt[2][2] + Mt[1][1]);
+            drot[2] = 2 * x * (Mt[1][0] + Mt[0][1]) + 2 * r * (Mt[2][0] - Mt[0][2]) + 2 * z * (Mt[1][2] + Mt[2][1]) - 4 * y * (Mt[2][2] + Mt[0][0]);
+            drot[3] = 2 * r * (Mt[0][1] - Mt[1][0]) + 2 * x * (Mt[2][0] + Mt[0][2]) + 2 * y * (Mt[1][2] + Mt[2][1]) - 4 * z * (Mt[1][1] + Mt[0][0]);
+        }
+    }
+
+    // ---- SH backward (backward.cu:20-139)
+    if (SH16) {
+        pre_cp_async_wait();
+        __syncthreads();
+    }
+    if (vis) {
         if (a.shs != nullptr || a.sh_dc != nullptr) {
             const uint8_t cbits = b.clamped[idx];
             dRGB[0] = (cbits & 1) ? 0.f : dcolor[0];
@@ -445,12 +518,12 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
             float sd[16];
             const int nb = (deg + 1) * (deg + 1);
             if (SH16) {
-                const float4* p4 = reinterpret_cast<const float4*>(a.shs + (size_t)idx * 48);
+                const float4* p4 = my_row;
                 float f[48];
 #pragma unroll
                 for (int k = 0; k < 12; k++) {
                     if (k * 4 < nb * 3) {
-                        float4 v = __ldg(p4 + k);
+                        float4 v = p4[k];
                         f[4 * k] = v.x; f[4 * k + 1] = v.y; f[4 * k + 2] = v.z; f[4 * k + 3] = v.w;
                     } else { f[4 * k] = f[4 * k + 1] = f[4 * k + 2] = f[4 * k + 3] = 0.f; }
                 }
@@ -503,85 +576,78 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
             dmean[1] += (-d0x * d0y * ddx + (s2 - d0y * d0y) * ddy - d0z * d0y * ddz) * inv;
             dmean[2] += (-d0x * d0z * ddx - d0y * d0z * ddy + (s2 - d0z * d0z) * ddz) * inv;
         }
-        // ---- cov3D -> scale / rotation (backward.cu:278-341)
-        if (a.scales != nullptr) {
-            const float r = q.x, x = q.y, y = q.z, z = q.w;
-            const float Rm[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
-                                    {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
-                                    {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
-            const float s[3] = {a.scale_modifier * sc[0], a.scale_modifier * sc[1], a.scale_modifier * sc[2]};
-            const float dS[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
-                                    {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
-                                    {0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
-            float Mt[3][3];   // reference's dL_dMt[a][b] (glm indexing) after scaling by s_a
-#pragma unroll
-            for (int i = 0; i < 3; i++) {
-                float dMi[3];
-#pragma unroll
-                for (int j = 0; j < 3; j++)
-                    dMi[j] = 2.0f * ((s[i] * Rm[0][i]) * dS[0][j] + (s[i] * Rm[1][i]) * dS[1][j] + (s[i] * Rm[2][i]) * dS[2][j]);
-                dscale[i] = Rm[0][i] * dMi[0] + Rm[1][i] * dMi[1] + Rm[2][i] * dMi[2];
-#pragma unroll
-                for (int j = 0; j < 3; j++) Mt[i][j] = s[i] * dMi[j];
-            }
-            drot[0] = 2 * z * (Mt[0][1] - Mt[1][0]) + 2 * y * (Mt[2][0] - Mt[0][2]) + 2 * x * (Mt[1][2] - Mt[2][1]);
-            drot[1] = 2 * y * (Mt[1][0] + Mt[0][1]) + 2 * z * (Mt[2][0] + Mt[0][2]) + 2 * r * (Mt[1][2] - Mt[2][1]) - 4 * x * (Mt[2][2] + Mt[1][1]);
-            drot[2] = 2 * x * (Mt[1][0] + Mt[0][1]) + 2 * r * (Mt[2][0] - Mt[0][2]) + 2 * z * (Mt[1][2] + Mt[2][1]) - 4 * y * (Mt[2][2] + Mt[0][0]);
-            drot[3] = 2 * r * (Mt[0][1] - Mt[1][0]) + 2 * x * (Mt[2][0] + Mt[0][2]) + 2 * y * (Mt[1][2] + Mt[2][1]) - 4 * z * (Mt[1][1] + Mt[0][0]);
-        }
     }
 
     // ---- write everything (zeros for invisible Gaussians); in accumulate mode add to what is there and leave the
     // rows of invisible Gaussians untouched (multi-view batches: no zero fill, no separate accumulation pass)
     const bool accum = o.accumulate != 0;
-    o.dL_dmeans2D[3 * (size_t)idx + 0] = dmean2d[0];     // per-view sink of the caller (train.py:159): never accumulated
-    o.dL_dmeans2D[3 * (size_t)idx + 1] = dmean2d[1];
-    o.dL_dmeans2D[3 * (size_t)idx + 2] = 0.f;
-    if (o.dL_dconic)
-        reinterpret_cast<float4*>(o.dL_dconic)[idx] = make_float4(dconic[0], dconic[1], 0.f, dconic[2]);
-    if (accum && !vis) return;
-    auto put = [accum](float* p, float v) { *p = accum ? *p + v : v; };
-    auto put4 = [accum](float4* p, float4 v) {
-        if (accum) { const float4 c = *p; v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w; }
-        *p = v;
-    };
-    put(o.dL_dopacity + idx, dopac);
-#pragma unroll
-    for (int k = 0; k < 3; k++) put(o.dL_dmeans3D + 3 * (size_t)idx + k, dmean[k]);
-    if (o.dL_dcolors) {
-#pragma unroll
-        for (int k = 0; k < 3; k++) put(o.dL_dcolors + 3 * (size_t)idx + k, dcolor[k]);
+    if (inside) {
+        o.dL_dmeans2D[3 * (size_t)idx + 0] = dmean2d[0]; // per-view sink of the caller (train.py:159): never accumulated
+        o.dL_dmeans2D[3 * (size_t)idx + 1] = dmean2d[1];
+        o.dL_dmeans2D[3 * (size_t)idx + 2] = 0.f;
+        if (o.dL_dconic)
+            reinterpret_cast<float4*>(o.dL_dconic)[idx] = make_float4(dconic[0], dconic[1], 0.f, dconic[2]);
     }
-    if (o.dL_dcov3D) {
+    if (inside && !(accum && !vis)) {
+        auto put = [accum](float* p, float v) { *p = accum ? *p + v : v; };
+        auto put4 = [accum](float4* p, float4 v) {
+            if (accum) { const float4 c = *p; v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w; }
+            *p = v;
+        };
+        put(o.dL_dopacity + idx, dopac);
 #pragma unroll
-        for (int k = 0; k < 6; k++) put(o.dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
-    }
-    if (o.dL_dscales) {
+        for (int k = 0; k < 3; k++) put(o.dL_dmeans3D + 3 * (size_t)idx + k, dmean[k]);
+        if (o.dL_dcolors) {
 #pragma unroll
-        for (int k = 0; k < 3; k++) put(o.dL_dscales + 3 * (size_t)idx + k, dscale[k]);
-    }
-    if (o.dL_drotations) put4(reinterpret_cast<float4*>(o.dL_drotations) + idx, make_float4(drot[0], drot[1], drot[2], drot[3]));
-    if (o.dL_dsh || o.dL_ddc) {
-        if (SH16) {
-            float f[48];
+            for (int k = 0; k < 3; k++) put(o.dL_dcolors + 3 * (size_t)idx + k, dcolor[k]);
+        }
+        if (o.dL_dcov3D) {
 #pragma unroll
-            for (int k = 0; k < 16; k++) {
-                f[3 * k] = sh_coef[k] * dRGB[0]; f[3 * k + 1] = sh_coef[k] * dRGB[1]; f[3 * k + 2] = sh_coef[k] * dRGB[2];
+            for (int k = 0; k < 6; k++) put(o.dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
+        }
+        if (o.dL_dscales) {
+#pragma unroll
+            for (int k = 0; k < 3; k++) put(o.dL_dscales + 3 * (size_t)idx + k, dscale[k]);
+        }
+        if (o.dL_drotations) put4(reinterpret_cast<float4*>(o.dL_drotations) + idx, make_float4(drot[0], drot[1], drot[2], drot[3]));
+        if (o.dL_dsh || o.dL_ddc) {
+            if (SH16) {
+                if (vis) {
+                    // the row's gradient replaces its coefficients in shared memory; the CTA writes all rows out together
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const float c0 = sh_coef[4 * k], c1 = sh_coef[4 * k + 1], c2 = sh_coef[4 * k + 2], c3 = sh_coef[4 * k + 3];
+                        my_row[3 * k] = make_float4(c0 * dRGB[0], c0 * dRGB[1], c0 * dRGB[2], c1 * dRGB[0]);
+                        my_row[3 * k + 1] = make_float4(c1 * dRGB[1], c1 * dRGB[2], c2 * dRGB[0], c2 * dRGB[1]);
+                        my_row[3 * k + 2] = make_float4(c2 * dRGB[2], c3 * dRGB[0], c3 * dRGB[1], c3 * dRGB[2]);
+                    }
+                } else {                                   // culled, not accumulating: a zero row
+                    float4* dst = reinterpret_cast<float4*>(o.dL_dsh + (size_t)idx * 48);
+#pragma unroll
+                    for (int k = 0; k < 12; k++) dst[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            } else {
+                // accumulate mode: coefficients above the active degree have zero gradient and need no traffic
+                const int kmax = accum ? min(M, (a.D + 1) * (a.D + 1)) : M;
+                for (int k = 0; k < kmax; k++) {
+                    const float c = k < 16 ? sh_coef[k < 16 ? k : 0] : 0.f;
+                    float* dst = sh_ptr(o.dL_dsh, o.dL_ddc, idx, M, k);
+                    put(dst, c * dRGB[0]); put(dst + 1, c * dRGB[1]); put(dst + 2, c * dRGB[2]);
+                }
             }
-            float4* dst = reinterpret_cast<float4*>(o.dL_dsh + (size_t)idx * 48);
-            // coefficients above the active degree have zero gradient: in accumulate mode they need no traffic at all
-            const int nq = accum ? ((a.D + 1) * (a.D + 1) * 3 + 3) / 4 : 12;
-#pragma unroll
-            for (int k = 0; k < 12; k++)
-                if (k < nq) put4(dst + k, make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]));
-        } else {
-            // accumulate mode: coefficients above the active degree have zero gradient and need no traffic
-            const int kmax = accum ? min(M, (a.D + 1) * (a.D + 1)) : M;
-            for (int k = 0; k < kmax; k++) {
-                const float c = k < 16 ? sh_coef[k < 16 ? k : 0] : 0.f;
-                float* dst = sh_ptr(o.dL_dsh, o.dL_ddc, idx, M, k);
-                put(dst, c * dRGB[0]); put(dst + 1, c * dRGB[1]); put(dst + 2, c * dRGB[2]);
-            }
+        }
+    }
+    if (SH16) {
+        __syncthreads();
+        // coefficients above the active degree have zero gradient: in accumulate mode they need no traffic at all
+        const int nq = accum ? n_quads : 12;
+        float* dst0 = o.dL_dsh + (size_t)blockIdx.x * 256 * 48;
+        for (int f = threadIdx.x; f < n_vis * nq; f += 256) {
+            const int sl = f / nq, k = f - sl * nq;
+            float4 v = *reinterpret_cast<const float4*>(s_rows + sl * kShRow + 4 * k);
+            float4* d = reinterpret_cast<float4*>(dst0 + (size_t)s_owner[sl] * 48 + 4 * k);
+            if (accum) { const float4 c = *d; v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w; }
+            *d = v;
         }
     }
 }
@@ -611,8 +677,16 @@ int launch_preprocess_backward(const gsr_view& v, const GeomState& g, const int*
     b.radii = radii; b.clamped = g.clamped; b.acc = acc; b.have_invdepth = have_invdepth ? 1 : 0; b.out = out;
     const int blocks = (v.P + 255) / 256;
     const bool fast = sh16_fast(v) && out.dL_dsh != nullptr && (reinterpret_cast<uintptr_t>(out.dL_dsh) & 15) == 0;
-    if (fast)
-        GSR_LAUNCH("preprocess_bwd", v.debug, s, (preprocess_bwd_kernel<true><<<blocks, 256, 0, s>>>(b)));
+    if (fast) {
+        const int smem = 256 * kShRow * (int)sizeof(float);
+        static bool attr_set = false;                 // one process drives one device
+        if (!attr_set) {
+            cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            if (e != cudaSuccess) return (int)e;
+            attr_set = true;
+        }
+        GSR_LAUNCH("preprocess_bwd", v.debug, s, (preprocess_bwd_kernel<true><<<blocks, 256, smem, s>>>(b)));
+    }
     else
         GSR_LAUNCH("preprocess_bwd", v.debug, s, (preprocess_bwd_kernel<false><<<blocks, 256, 0, s>>>(b)));
     return 0;
