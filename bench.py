@@ -385,8 +385,7 @@ def work_model(arm, args):
         "digit_hist": ("hbm", 4.0 * (4 * P + rp * R)),
         "digit_scan": ("hbm", 8.0 * 256 * (4 * sort_tiles_P + rp * sort_tiles_R)),
         "digit_scatter": ("hbm", 16.0 * (4 * P + rp * R)),
-        "scan_reduce": ("hbm", 8.0 * P), "scan_spine": ("hbm", 8.0 * ((P + 2047) // 2048)),
-        "scan_apply": ("hbm", 12.0 * P),
+        "scan_chained": ("hbm", 12.0 * P),
         "emit_instances": ("hbm", 8.0 * P + 28.0 * visible + 8.0 * R),
         "tile_ranges": ("hbm", 4.0 * R + 8.0 * tiles),
         # 13 flop for every (pixel, list entry) pair the reference iterates (power + alpha test);

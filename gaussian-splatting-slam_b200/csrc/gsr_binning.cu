@@ -11,7 +11,7 @@
 
 namespace gsr {
 
-// ------------------------------------------------------------------ scan (3 launches, no spinning)
+// ------------------------------------------------------------------ scan
 constexpr int kScanThreads = 256;
 constexpr int kScanItems = GSR_SCAN_TILE / kScanThreads;   // 8, blocked per thread
 
@@ -37,46 +37,22 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* w
     return woff + incl - v;
 }
 
-__global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(const uint32_t* __restrict__ counts,
-                                                                    const uint32_t* __restrict__ order, int n,
-                                                                    uint32_t* __restrict__ sums) {
+// Single-pass chained scan (decoupled look-back) of tiles_touched in depth order: one launch instead of
+// reduce / spine / apply. A tile's status word carries flag (bits 30-31: 1 = the tile's own sum, 2 = inclusive prefix)
+// and value (30 bits: num_rendered < 2^30 is enforced by the caller) together, so one 32-bit store publishes both.
+// Tiles are taken by ticket, which makes waiting on lower-numbered tiles safe whatever the CTA scheduling order.
+// status[0..m) = tile words, status[m] = grand total, status[m + 1] = ticket; all zeroed before the launch.
+constexpr uint32_t kScanOwn = 1u << 30, kScanIncl = 2u << 30, kScanVal = (1u << 30) - 1u;
+__global__ void __launch_bounds__(kScanThreads) scan_chained_kernel(const uint32_t* __restrict__ counts,
+                                                                     const uint32_t* __restrict__ order, int n, int m,
+                                                                     uint32_t* __restrict__ status,
+                                                                     uint32_t* __restrict__ out) {
     __shared__ uint32_t warp_sums[kScanThreads / 32];
-    const int base = blockIdx.x * GSR_SCAN_TILE + threadIdx.x * kScanItems;
-    uint32_t v = 0;
-#pragma unroll
-    for (int i = 0; i < kScanItems; i++)
-        if (base + i < n) v += __ldg(counts + __ldg(order + base + i));
-    uint32_t total;
-    block_exclusive_scan(v, warp_sums, total);
-    if (threadIdx.x == 0) sums[blockIdx.x] = total;
-}
-
-// single block: exclusive scan of sums[0..m) in place; sums[m] = grand total
-__global__ void __launch_bounds__(kScanThreads) scan_spine_kernel(uint32_t* __restrict__ sums, int m) {
-    __shared__ uint32_t warp_sums[kScanThreads / 32];
-    __shared__ uint32_t s_carry;
-    if (threadIdx.x == 0) s_carry = 0;
+    __shared__ uint32_t s_tile, s_prefix;
+    if (threadIdx.x == 0) s_tile = atomicAdd(status + m + 1, 1u);
     __syncthreads();
-    for (int c0 = 0; c0 < m; c0 += kScanThreads) {
-        const int i = c0 + threadIdx.x;
-        const uint32_t x = i < m ? sums[i] : 0u;
-        uint32_t total;
-        const uint32_t ex = block_exclusive_scan(x, warp_sums, total);
-        const uint32_t carry = s_carry;
-        if (i < m) sums[i] = carry + ex;
-        __syncthreads();
-        if (threadIdx.x == 0) s_carry = carry + total;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) sums[m] = s_carry;
-}
-
-__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint32_t* __restrict__ counts,
-                                                                   const uint32_t* __restrict__ order, int n,
-                                                                   const uint32_t* __restrict__ sums,
-                                                                   uint32_t* __restrict__ out) {
-    __shared__ uint32_t warp_sums[kScanThreads / 32];
-    const int base = blockIdx.x * GSR_SCAN_TILE + threadIdx.x * kScanItems;
+    const int tile = (int)s_tile;
+    const int base = tile * GSR_SCAN_TILE + threadIdx.x * kScanItems;
     uint32_t c[kScanItems], v = 0;
 #pragma unroll
     for (int i = 0; i < kScanItems; i++) {
@@ -84,7 +60,35 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint32_t
         v += c[i];
     }
     uint32_t total;
-    uint32_t run = block_exclusive_scan(v, warp_sums, total) + sums[blockIdx.x];
+    const uint32_t ex = block_exclusive_scan(v, warp_sums, total);
+    volatile uint32_t* vs = status;
+    if (threadIdx.x == 0) vs[tile] = (tile == 0 ? kScanIncl : kScanOwn) | total;
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        uint32_t prefix = 0;
+        for (int j = tile - 1; j >= 0; j -= 32) {
+            const int idx = j - lane;
+            uint32_t st = kScanIncl;                       // before the first tile: inclusive prefix 0
+            if (idx >= 0) {
+                st = vs[idx];
+                while ((st >> 30) == 0u) { __nanosleep(20); st = vs[idx]; }
+            }
+            const unsigned incl = __ballot_sync(0xffffffffu, (st >> 30) == 2u);
+            const int first = incl ? __ffs(incl) - 1 : 31;
+            uint32_t val = lane <= first ? (st & kScanVal) : 0u;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+            prefix += val;
+            if (incl) break;
+        }
+        if (lane == 0) {
+            if (tile > 0) vs[tile] = kScanIncl | (prefix + total);
+            if (tile == m - 1) status[m] = prefix + total;
+            s_prefix = prefix;
+        }
+    }
+    __syncthreads();
+    uint32_t run = ex + s_prefix;
 #pragma unroll
     for (int i = 0; i < kScanItems; i++) {
         run += c[i];
@@ -95,15 +99,13 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint32_t
 int launch_order_and_scan(const gsr_view& v, GeomState& g, uint32_t** total_dev, cudaStream_t s) {
     const int P = v.P;
     bool in_a = true;
+    GSR_MEMSET("memset_scan", s, g.scan_sums, 0, sizeof(uint32_t) * ((size_t)(P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE + 8));
     int e = radix_sort_u32(g.dkey, g.order, g.dkey_tmp, g.order_tmp, P, 32, g.sort_scratch, &in_a, v.debug != 0, s);
     if (e) return e;
     // 4 passes: the result is back in (dkey, order)
     const int m = (P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE;
-    GSR_LAUNCH("scan_reduce", v.debug, s,
-               (scan_reduce_kernel<<<m, kScanThreads, 0, s>>>(g.tiles_touched, g.order, P, g.scan_sums)));
-    GSR_LAUNCH("scan_spine", v.debug, s, (scan_spine_kernel<<<1, kScanThreads, 0, s>>>(g.scan_sums, m)));
-    GSR_LAUNCH("scan_apply", v.debug, s,
-               (scan_apply_kernel<<<m, kScanThreads, 0, s>>>(g.tiles_touched, g.order, P, g.scan_sums, g.point_offsets)));
+    GSR_LAUNCH("scan_chained", v.debug, s,
+               (scan_chained_kernel<<<m, kScanThreads, 0, s>>>(g.tiles_touched, g.order, P, m, g.scan_sums, g.point_offsets)));
     *total_dev = g.scan_sums + m;
     return 0;
 }
