@@ -381,10 +381,10 @@ def work_model(arm, args):
     w = {
         # per visible Gaussian 311 B (read 236 + write 75), per culled one 20 B
         "preprocess_fwd": ("hbm", 311.0 * visible + 20.0 * (P - visible)),
-        # (P-sort: 4 passes) + (R-sort: rp passes): hist reads 4 B/key, scatter reads 8 + writes 8 B/pair
-        "digit_hist": ("hbm", 4.0 * (4 * P + rp * R)),
-        "digit_scan": ("hbm", 8.0 * 256 * (4 * sort_tiles_P + rp * sort_tiles_R)),
-        "digit_scatter": ("hbm", 16.0 * (4 * P + rp * R)),
+        # (P-sort: 4 passes) + (R-sort: rp passes): one histogram read of the keys per sort, then 8 B read + 8 B written
+        # per pair and pass
+        "radix_hist": ("hbm", 4.0 * (P + R)),
+        "onesweep_pass": ("hbm", 16.0 * (4 * P + rp * R)),
         "scan_chained": ("hbm", 12.0 * P),
         "emit_instances": ("hbm", 8.0 * P + 28.0 * visible + 8.0 * R),
         "tile_ranges": ("hbm", 4.0 * R + 8.0 * tiles),

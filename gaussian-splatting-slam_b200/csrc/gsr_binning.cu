@@ -137,8 +137,8 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint32
     int x0 = 0, y0 = 0, bw = 1;
     if (j < P) {
         g = __ldg(order + j);
-        n = __ldg(tiles_touched + g);
         end = __ldg(offsets + j);                   // inclusive scan in depth order
+        n = end - (j > 0 ? __ldg(offsets + j - 1) : 0u);   // = tiles_touched[g], without the gather
         if (n > 0) {
             int x1, y1;
             const float4 r0 = __ldg(rec + 3 * (size_t)g);
