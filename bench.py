@@ -513,6 +513,7 @@ def _main(out_fd):
         arm = ReferenceArm(args, sc, cams, dpix_host, dev)
     else:
         arm = OursArm(args, sc, cams, dpix_host, dev)
+    exchange_kind = getattr(getattr(arm, "bucket", None), "exchange", "collective")
 
     def barrier():
         if ref_world > 1:
@@ -626,6 +627,10 @@ def _main(out_fd):
         cb = cpu_baseline(args)
 
     if rank == 0:
+        kind = exchange_kind
+        exchange_desc = {"multimem": "gsr_allreduce_sum launch per rank (NVSwitch multicast reduction over symmetric memory)",
+                         "peer": "gsr_allreduce_sum launch per rank (NVLink peer loads/stores over symmetric memory)"}.get(
+                             kind, "NCCL all-reduce")
         out = {"metric": METRIC, "value": round(value, 3), "unit": "views/s", "n_gpus": ref_world, "steps": args.steps,
                "warmup": args.warmup, "warmup_steps_run": warm_run, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -636,7 +641,7 @@ def _main(out_fd):
                                        " + fused L1/SSIM loss per view + one Adam step over all parameters per step (full train-step)"),
                           "views_per_step_per_gpu": args.views_per_step, "global_views_per_step": args.views_per_step * ref_world,
                           "parallelism": f"view-parallel dp{ref_world}, replicated Gaussians" +
-                                         (", NCCL all-reduce of 59 floats/Gaussian per step" if ref_world > 1 else ""),
+                                         (f", one {exchange_desc} of 59 floats/Gaussian per step" if ref_world > 1 else ""),
                           "l2": "inputs (708 MB parameters + 300 MB scratch per view) exceed the 126 MB L2; no explicit flush"},
                "step_ms_min_med_max": [round(step_ms[0], 3), round(step_ms[len(step_ms) // 2], 3), round(step_ms[-1], 3)],
                "clocks": clocks, "gpu_launches": launches,

@@ -11,7 +11,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgsr.so")
-SOURCES = ["gsr_api.cu", "gsr_preprocess.cu", "gsr_sort.cu", "gsr_binning.cu", "gsr_blend.cu", "gsr_knn.cu", "gsr_ssim.cu", "gsr_adam.cu", "gsr_densify.cu"]
+SOURCES = ["gsr_api.cu", "gsr_preprocess.cu", "gsr_sort.cu", "gsr_binning.cu", "gsr_blend.cu", "gsr_knn.cu", "gsr_ssim.cu", "gsr_adam.cu", "gsr_densify.cu", "gsr_comm.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC"]

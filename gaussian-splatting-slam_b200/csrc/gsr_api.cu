@@ -308,6 +308,30 @@ int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, doub
     return launch_adam(groups, n_groups, beta1, beta2, eps, visible, (cudaStream_t)stream);
 }
 
+size_t gsr_comm_signal_bytes(void) { return sizeof(uint32_t) * GSR_COMM_MAX_CTAS * GSR_COMM_MAX_PEERS; }
+
+int gsr_comm_slice(long long numel, int rank, int world, long long* lo, long long* hi) {
+    if (numel < 0 || (numel & 3) || world < 1 || world > GSR_COMM_MAX_PEERS || rank < 0 || rank >= world || !lo || !hi)
+        return GSR_E_BADARG;
+    comm_slice(numel / 4, rank, world, lo, hi);
+    *lo *= 4;
+    *hi *= 4;
+    return 0;
+}
+
+int gsr_allreduce_sum(const gsr_peer_group* group, long long numel, int max_ctas, void* stream) {
+    if (!group || numel < 0 || (numel & 3) || max_ctas < 0) return GSR_E_BADARG;
+    const gsr_peer_group& g = *group;
+    if (g.world < 1 || g.world > GSR_COMM_MAX_PEERS || g.rank < 0 || g.rank >= g.world) return GSR_E_BADARG;
+    if (numel / 4 > (1ll << 40)) return GSR_E_TOOLARGE;
+    if (numel == 0) return 0;
+    for (int p = 0; p < g.world; p++)
+        if (!g.buf[p] || !g.signal[p] || (reinterpret_cast<uintptr_t>(g.buf[p]) & 15) || (reinterpret_cast<uintptr_t>(g.signal[p]) & 3))
+            return GSR_E_BADARG;
+    if (reinterpret_cast<uintptr_t>(g.multicast) & 15) return GSR_E_BADARG;
+    return launch_allreduce_sum(g, numel, max_ctas, (cudaStream_t)stream);
+}
+
 size_t gsr_densify_plan_bytes(int P) { return P < 0 ? 0 : densify_plan_bytes((size_t)P); }
 
 int gsr_densify_plan(int P, const float* opacity, const float* scaling, const float* grad_accum, const float* denom,

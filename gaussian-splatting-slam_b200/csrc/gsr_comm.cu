@@ -1,0 +1,169 @@
+// gsr_comm.cu -- the exchange step of view-parallel training: the sum all-reduce of the per-Gaussian
+// gradient bucket (59 floats = 236 B per Gaussian at SH degree 3; 708 MB at 3M), written directly against NVLink peer
+// memory instead of a library collective. The reference is single-GPU (train.py never leaves cuda:0), so there is no
+// reference function to replace; the contract is sum over ranks of the flat fp32 bucket, identical bits on all ranks.
+//
+// ONE launch per rank does the whole exchange:
+//   barrier   every CTA meets its twin (same blockIdx) on every peer through a signal pad in peer memory, so
+//             the peers' buckets are complete (their backward kernels precede this launch in stream order);
+//   reduce    rank r owns the r-th 1/world slice of the bucket. With an NVSwitch multicast mapping one
+//             multimem.ld_reduce pulls the slice with the addition done inside the switch and one multimem.st
+//             pushes the sum into every replica (each byte crosses each link once per direction). Without
+//             multicast, the slice is read from every peer's replica with 16-byte system-scope loads, added in
+//             rank order (so every rank holds the same bits) and written to every replica with peer stores;
+//   barrier   the same twins meet again once their stores are released, so when the kernel ends on a rank, all
+//             of its bucket has arrived.
+// No staging buffer, no copy kernels: the autograd .grad tensors ARE the peer-mapped bucket (view_parallel.py).
+// Bound: NVLink -- per rank (world-1)/world of the bucket leaves and enters through the switch.
+#include "gsr_common.cuh"
+#include <cuda/atomic>
+
+namespace gsr {
+
+constexpr int kCommThreads = 512;
+constexpr int kCommUnroll = 4;          // 16-byte requests in flight per thread and peer
+
+struct CommArgs {
+    float4* buf[GSR_COMM_MAX_PEERS];
+    uint32_t* sig[GSR_COMM_MAX_PEERS];
+    float4* mc;
+    int rank, world;
+    long long lo, hi;                   // this rank's slice in 16-byte units
+};
+
+// signal pad protocol: slot (cta, source rank) on the destination's pad goes 0 -> 1 by the source, 1 -> 0 by the owner
+__device__ __forceinline__ void sig_put(uint32_t* slot) {
+    cuda::atomic_ref<uint32_t, cuda::thread_scope_system> ref(*slot);
+    uint32_t expect = 0;
+    while (!ref.compare_exchange_strong(expect, 1u, cuda::std::memory_order_release, cuda::std::memory_order_relaxed)) expect = 0;
+}
+__device__ __forceinline__ void sig_wait(uint32_t* slot) {
+    cuda::atomic_ref<uint32_t, cuda::thread_scope_system> ref(*slot);
+    uint32_t expect = 1;
+    while (!ref.compare_exchange_strong(expect, 0u, cuda::std::memory_order_acquire, cuda::std::memory_order_relaxed)) expect = 1;
+}
+__device__ __forceinline__ void twin_barrier(const CommArgs& a) {
+    __threadfence_system();
+    __syncthreads();
+    if ((int)threadIdx.x < a.world) {
+        const int peer = threadIdx.x;
+        sig_put(a.sig[peer] + (size_t)blockIdx.x * GSR_COMM_MAX_PEERS + a.rank);
+        sig_wait(a.sig[a.rank] + (size_t)blockIdx.x * GSR_COMM_MAX_PEERS + peer);
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 mc_ld_reduce(const float4* p) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st(float4* p, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 peer_ld(const float4* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void peer_st(float4* p, float4 v) {
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+template <bool MULTICAST, int WORLD>
+__global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_kernel(const __grid_constant__ CommArgs a) {
+    twin_barrier(a);
+    const long long stride = (long long)gridDim.x * kCommThreads;
+    const int world = WORLD > 0 ? WORLD : a.world;
+    for (long long i0 = a.lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < a.hi; i0 += stride * kCommUnroll) {
+        float4 v[kCommUnroll];
+        if (MULTICAST) {
+#pragma unroll
+            for (int u = 0; u < kCommUnroll; u++)
+                if (i0 + u * stride < a.hi) v[u] = mc_ld_reduce(a.mc + i0 + u * stride);
+#pragma unroll
+            for (int u = 0; u < kCommUnroll; u++)
+                if (i0 + u * stride < a.hi) mc_st(a.mc + i0 + u * stride, v[u]);
+        } else {
+            float4 w[kCommUnroll];
+#pragma unroll
+            for (int u = 0; u < kCommUnroll; u++)
+                if (i0 + u * stride < a.hi) v[u] = peer_ld(a.buf[0] + i0 + u * stride);
+#pragma unroll
+            for (int p = 1; p < (WORLD > 0 ? WORLD : GSR_COMM_MAX_PEERS); p++) {
+                if (p < world) {
+#pragma unroll
+                    for (int u = 0; u < kCommUnroll; u++)
+                        if (i0 + u * stride < a.hi) w[u] = peer_ld(a.buf[p] + i0 + u * stride);
+#pragma unroll
+                    for (int u = 0; u < kCommUnroll; u++) {      // rank order: the same bits on every rank
+                        v[u].x = __fadd_rn(v[u].x, w[u].x); v[u].y = __fadd_rn(v[u].y, w[u].y);
+                        v[u].z = __fadd_rn(v[u].z, w[u].z); v[u].w = __fadd_rn(v[u].w, w[u].w);
+                    }
+                }
+            }
+#pragma unroll
+            for (int p = 0; p < (WORLD > 0 ? WORLD : GSR_COMM_MAX_PEERS); p++) {
+                if (p < world) {
+#pragma unroll
+                    for (int u = 0; u < kCommUnroll; u++)
+                        if (i0 + u * stride < a.hi) peer_st(a.buf[p] + i0 + u * stride, v[u]);
+                }
+            }
+        }
+    }
+    twin_barrier(a);
+}
+
+void comm_slice(long long n16, int rank, int world, long long* lo, long long* hi) {
+    const long long per = (n16 + world - 1) / world;
+    const long long l = per * rank < n16 ? per * rank : n16;
+    const long long h = l + per < n16 ? l + per : n16;
+    *lo = l;
+    *hi = h;
+}
+
+int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas, cudaStream_t s) {
+    CommArgs a;
+    for (int p = 0; p < GSR_COMM_MAX_PEERS; p++) {
+        a.buf[p] = p < g.world ? reinterpret_cast<float4*>(g.buf[p]) : nullptr;
+        a.sig[p] = p < g.world ? g.signal[p] : nullptr;
+    }
+    a.mc = reinterpret_cast<float4*>(g.multicast);
+    a.rank = g.rank;
+    a.world = g.world;
+    const long long n16 = numel / 4;
+    comm_slice(n16, g.rank, g.world, &a.lo, &a.hi);
+    // the grid must be the same on every rank (CTAs meet their twins): derive it from the largest slice only
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return (int)e;
+    }
+    const long long per = (n16 + g.world - 1) / g.world;
+    long long ctas = (per + (long long)kCommThreads * kCommUnroll - 1) / ((long long)kCommThreads * kCommUnroll);
+    long long cap = max_ctas > 0 ? max_ctas : 2 * sms;
+    if (cap > GSR_COMM_MAX_CTAS) cap = GSR_COMM_MAX_CTAS;
+    if (ctas > cap) ctas = cap;
+    if (ctas < 1) ctas = 1;
+    const unsigned grid = (unsigned)ctas;
+    if (a.mc != nullptr)
+        GSR_LAUNCH("allreduce_sum_multimem", false, s, (allreduce_sum_kernel<true, 0><<<grid, kCommThreads, 0, s>>>(a)));
+    else if (g.world == 2)
+        GSR_LAUNCH("allreduce_sum_peer", false, s, (allreduce_sum_kernel<false, 2><<<grid, kCommThreads, 0, s>>>(a)));
+    else if (g.world == 4)
+        GSR_LAUNCH("allreduce_sum_peer", false, s, (allreduce_sum_kernel<false, 4><<<grid, kCommThreads, 0, s>>>(a)));
+    else if (g.world == 8)
+        GSR_LAUNCH("allreduce_sum_peer", false, s, (allreduce_sum_kernel<false, 8><<<grid, kCommThreads, 0, s>>>(a)));
+    else
+        GSR_LAUNCH("allreduce_sum_peer", false, s, (allreduce_sum_kernel<false, 0><<<grid, kCommThreads, 0, s>>>(a)));
+    return 0;
+}
+
+}  // namespace gsr

@@ -167,6 +167,8 @@ int set_exact_cull(int on);
 int launch_cull_stats(const gsr_view& v, const GeomState& g, const BinningState& b, const ImageState& img,
                       unsigned long long* out, cudaStream_t s);
 int launch_adam(const gsr_adam_group* groups, int n, double b1, double b2, double eps, const uint8_t* visible, cudaStream_t s);
+int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas, cudaStream_t s);
+void comm_slice(long long n16, int rank, int world, long long* lo, long long* hi);
 int launch_exp_check(unsigned long long* mismatches_dev, cudaStream_t s);
 int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s);
 size_t dist2_temp_bytes(int P);

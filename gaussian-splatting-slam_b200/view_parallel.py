@@ -6,13 +6,96 @@ all-reduce of the per-Gaussian parameter gradients (59 floats = 236 B per Gaussi
 before the (identical) optimiser step. There is no data-path collective inside the rasterizer itself.
 
 The gradients live in one flat fp32 bucket (`GradBucket`): the parameters' .grad tensors are views into it, so the
-exchange is a single collective over one contiguous buffer with no packing copies, and zeroing is one memset.
-Works with any torch.distributed backend (NCCL over NVLink on the GPU box; gloo in the CPU tests).
+exchange is a single step over one contiguous buffer with no packing copies, and zeroing is one memset.
+
+The exchange itself (`GradBucket.all_reduce`):
+  * on CUDA ranks of one NVLink box the bucket is allocated as symmetric memory (every rank maps every other rank's
+    bucket, plus the NVSwitch multicast mapping when the fabric offers one) and the step is ONE launch of libgsr's own
+    kernel per rank (`gsr_allreduce_sum`, csrc/gsr_comm.cu): in-switch reduction with multimem.ld_reduce /
+    multimem.st, or peer loads + peer stores without multicast. The autograd .grad tensors ARE that peer-mapped memory;
+  * otherwise (gloo in the CPU tests, `GSR_EXCHANGE=nccl`, or a box where peer mapping cannot be set up) one
+    torch.distributed all-reduce over the same flat buffer.
+`GSR_EXCHANGE` = auto (default) | multimem | peer | nccl selects the path; anything but auto fails loudly when the
+requested path is unavailable.
 """
+import ctypes as C
+import os
+import sys
 from typing import Dict, List, Sequence
 
 import torch
 import torch.distributed as dist
+
+GSR_COMM_MAX_PEERS = 16
+
+
+class _PeerGroup(C.Structure):      # gsr_peer_group (include/gsr.h)
+    _fields_ = [("rank", C.c_int), ("world", C.c_int), ("buf", C.c_void_p * GSR_COMM_MAX_PEERS),
+                ("signal", C.c_void_p * GSR_COMM_MAX_PEERS), ("multicast", C.c_void_p)]
+
+
+def _gsr():
+    from diff_gaussian_rasterization import _C
+    L = _C.lib()
+    if not getattr(L, "_comm_bound", False):
+        L.gsr_comm_signal_bytes.restype = C.c_size_t
+        L.gsr_comm_slice.restype = C.c_int
+        L.gsr_comm_slice.argtypes = [C.c_longlong, C.c_int, C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
+        L.gsr_allreduce_sum.restype = C.c_int
+        L.gsr_allreduce_sum.argtypes = [C.POINTER(_PeerGroup), C.c_longlong, C.c_int, C.c_void_p]
+        L._comm_bound = True
+    return L, _C
+
+
+def comm_slice(numel: int, rank: int, world: int):
+    """[lo, hi) of the bucket that `rank` reduces in gsr_allreduce_sum (host helper of the C ABI)."""
+    L, _C = _gsr()
+    lo, hi = C.c_longlong(0), C.c_longlong(0)
+    _C._check(L.gsr_comm_slice(numel, rank, world, C.byref(lo), C.byref(hi)), "gsr_comm_slice")
+    return lo.value, hi.value
+
+
+def peer_all_reduce(group_desc: "_PeerGroup", numel: int, max_ctas: int = 0, stream=None):
+    """One launch of the exchange kernel on `stream` (default: torch's current stream)."""
+    L, _C = _gsr()
+    st = torch.cuda.current_stream().cuda_stream if stream is None else stream
+    _C._check(L.gsr_allreduce_sum(C.byref(group_desc), numel, max_ctas, C.c_void_p(st)), "gsr_allreduce_sum")
+
+
+class PeerExchange:
+    """Flat fp32 buffer in symmetric memory + the descriptor gsr_allreduce_sum needs. Collective constructor."""
+
+    def __init__(self, numel: int, device, group=None, multicast=True):
+        import torch.distributed._symmetric_memory as symm_mem
+        L, _ = _gsr()
+        group = group if group is not None else dist.group.WORLD
+        if numel % 4:
+            raise ValueError("peer exchange needs a multiple of 4 elements")
+        self.flat = symm_mem.empty(numel, dtype=torch.float32, device=device)
+        self.hdl = symm_mem.rendezvous(self.flat, group)
+        self.signal = symm_mem.empty(L.gsr_comm_signal_bytes() // 4, dtype=torch.int32, device=device)
+        self.signal.zero_()
+        self.sig_hdl = symm_mem.rendezvous(self.signal, group)
+        self.flat.zero_()
+        torch.cuda.synchronize(device)
+        dist.barrier(group)                        # every pad is zero before anybody signals
+        h, sh = self.hdl, self.sig_hdl
+        if h.world_size > GSR_COMM_MAX_PEERS:
+            raise RuntimeError(f"peer exchange supports up to {GSR_COMM_MAX_PEERS} ranks")
+        g = _PeerGroup()
+        g.rank, g.world = h.rank, h.world_size
+        off = self.flat.data_ptr() - int(h.buffer_ptrs[h.rank])         # the tensor may sit inside a pooled block
+        soff = self.signal.data_ptr() - int(sh.buffer_ptrs[sh.rank])
+        for p in range(h.world_size):
+            g.buf[p] = int(h.buffer_ptrs[p]) + off
+            g.signal[p] = int(sh.buffer_ptrs[p]) + soff
+        mc = int(h.multicast_ptr) if multicast else 0
+        g.multicast = (mc + off) if mc else None
+        self.desc, self.numel, self.has_multicast = g, numel, bool(mc)
+        self.kind = "multimem" if mc else "peer"
+
+    def all_reduce(self, max_ctas: int = 0):
+        peer_all_reduce(self.desc, self.numel, max_ctas)
 
 
 def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
@@ -25,7 +108,7 @@ def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
 class GradBucket:
     """Flat gradient storage for a dict of leaf parameters."""
 
-    def __init__(self, params: Dict[str, torch.Tensor]):
+    def __init__(self, params: Dict[str, torch.Tensor], exchange: str = None, group=None):
         if not params:
             raise ValueError("GradBucket needs at least one parameter")
         dev = {p.device for p in params.values()}
@@ -41,9 +124,38 @@ class GradBucket:
                 raise ValueError(f"{name}: gradients are exchanged in fp32")
             self.offsets[name] = off
             off += (n + 31) // 32 * 32
-        self.flat = torch.zeros(off, dtype=torch.float32, device=self.device)
+        self.peer, self.exchange = None, "collective"
+        mode = (exchange or os.environ.get("GSR_EXCHANGE", "auto")).lower()
+        if mode not in ("auto", "multimem", "peer", "nccl"):
+            raise ValueError(f"GSR_EXCHANGE={mode}: expected auto, multimem, peer or nccl")
+        multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+        if multi and self.device.type == "cuda" and mode != "nccl":
+            self.peer = self._try_peer(off, mode, group)
+        if self.peer is not None:
+            self.flat, self.exchange = self.peer.flat, self.peer.kind
+        else:
+            self.flat = torch.zeros(off, dtype=torch.float32, device=self.device)
         self.views = {name: self.flat[o:o + p.numel()].view_as(p) for (name, p), o in
                       zip(self.params.items(), self.offsets.values())}
+
+    def _try_peer(self, numel, mode, group):
+        """Sets the peer-memory exchange up on all ranks or on none (the ranks agree through a MIN all-reduce)."""
+        px, err = None, None
+        try:
+            px = PeerExchange(numel, self.device, group, multicast=(mode != "peer"))
+            if mode == "multimem" and not px.has_multicast:
+                raise RuntimeError("no NVSwitch multicast mapping for the bucket")
+        except Exception as e:          # noqa: BLE001 - any set-up failure means "not available here"
+            px, err = None, e
+        ok = torch.tensor([1 if px is not None else 0], device=self.device, dtype=torch.int32)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if int(ok.item()) == 1:
+            return px
+        if mode != "auto":
+            raise RuntimeError(f"GSR_EXCHANGE={mode} requested but peer memory could not be set up: {err}")
+        if dist.get_rank(group) == 0:
+            print(f"[view_parallel] peer-memory exchange unavailable ({err}); using the backend's all-reduce", file=sys.stderr)
+        return None
 
     def attach(self):
         """Points every parameter's .grad at its slice of the bucket (autograd then accumulates in place)."""
@@ -59,6 +171,11 @@ class GradBucket:
     def all_reduce(self, group=None, async_op=False, average=False):
         """The exchange step: sum (optionally mean) of the bucket over all ranks."""
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return None
+        if self.peer is not None:
+            self.peer.all_reduce()                  # one launch on the current stream; stream order is the only sync
+            if average:
+                self.flat.div_(dist.get_world_size(group))
             return None
         work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
         if average and not async_op:

@@ -88,3 +88,39 @@ def test_two_ranks_equal_one_rank(tmp_path, n_views):
     assert torch.allclose(got["flat"], bk.flat, rtol=1e-5, atol=1e-6)
     assert torch.equal(got["acc"], torch.full((4,), 3.0)) and torch.equal(got["den"], torch.full((4,), 2.0))
     assert torch.equal(got["mx"], torch.tensor([2.0, 10.0, 4.0, 0.0]))
+
+
+def test_comm_slices_partition_the_bucket_and_bad_arguments_are_refused(gsr_lib):
+    """Host side of the peer-memory exchange (include/gsr.h: gsr_comm_slice, gsr_allreduce_sum): every rank's slice is
+    16-byte granular, the slices are disjoint and cover the bucket; malformed groups never reach a launch."""
+    import ctypes as C
+    from view_parallel import _PeerGroup, comm_slice, _gsr
+    L, _ = _gsr()
+    for numel in (0, 4, 36, 4096, 3_000_000 * 59 // 4 * 4, 177_000_032):
+        for world in (1, 2, 3, 4, 8, 16):
+            parts = [comm_slice(numel, r, world) for r in range(world)]
+            assert parts[0][0] == 0 and parts[-1][1] == numel
+            assert all(lo % 4 == 0 and hi % 4 == 0 and lo <= hi for lo, hi in parts)
+            assert all(parts[r][1] == parts[r + 1][0] for r in range(world - 1))
+            assert max(hi - lo for lo, hi in parts) <= (numel // 4 + world - 1) // world * 4
+    lo, hi = C.c_longlong(), C.c_longlong()
+    assert L.gsr_comm_slice(6, 0, 2, C.byref(lo), C.byref(hi)) == -1          # not a multiple of 4
+    assert L.gsr_comm_slice(8, 2, 2, C.byref(lo), C.byref(hi)) == -1          # rank outside the group
+    assert L.gsr_comm_slice(8, 0, 17, C.byref(lo), C.byref(hi)) == -1         # more peers than GSR_COMM_MAX_PEERS
+    assert L.gsr_comm_signal_bytes() == 4 * 512 * 16
+    g = _PeerGroup()
+    g.rank, g.world = 0, 2
+    assert L.gsr_allreduce_sum(C.byref(g), 1024, 0, None) == -1               # NULL peer mappings
+    assert L.gsr_allreduce_sum(None, 1024, 0, None) == -1
+    g.buf[0], g.buf[1], g.signal[0], g.signal[1] = 4096, 8200, 4096, 4096
+    assert L.gsr_allreduce_sum(C.byref(g), 1024, 0, None) == -1               # buf[1] not 16-byte aligned
+    g.buf[1] = 8192
+    assert L.gsr_allreduce_sum(C.byref(g), 1022, 0, None) == -1               # numel not a multiple of 4
+    assert L.gsr_allreduce_sum(C.byref(g), 0, 0, None) == 0                   # empty bucket: nothing to launch
+
+
+def test_grad_bucket_exchange_mode_is_validated():
+    p = {"a": torch.randn(4, requires_grad=True)}
+    assert GradBucket(p).exchange == "collective"
+    with pytest.raises(ValueError):
+        GradBucket(p, exchange="carrier-pigeon")
