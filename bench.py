@@ -471,6 +471,15 @@ def main():
         os.dup2(real_stdout, 1)
 
 
+def _physical_gpu_index(local):
+    """NVML enumerates all GPUs of the box; CUDA_VISIBLE_DEVICES may have re-numbered ours."""
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+    ids = [v.strip() for v in vis.split(",") if v.strip()]
+    if local < len(ids) and ids[local].isdigit():
+        return int(ids[local])
+    return local
+
+
 def emit(fd, obj):
     os.write(fd, (json.dumps(obj) + "\n").encode())
 
@@ -495,6 +504,10 @@ def _main(out_fd):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     import torch.distributed as dist
+    bound_cpus = None
+    if world > 1 and args.impl == "ours" and os.environ.get("GSR_NUMA_BIND", "1") != "0":
+        from view_parallel import bind_rank_to_gpu_numa      # pinned host buffers next to the rank's GPU
+        bound_cpus = bind_rank_to_gpu_numa(_physical_gpu_index(local))
     ref_world = 1 if args.impl == "reference" else world
     if ref_world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -645,6 +658,8 @@ def _main(out_fd):
                           "l2": "inputs (708 MB parameters + 300 MB scratch per view) exceed the 126 MB L2; no explicit flush"},
                "step_ms_min_med_max": [round(step_ms[0], 3), round(step_ms[len(step_ms) // 2], 3), round(step_ms[-1], 3)],
                "clocks": clocks, "gpu_launches": launches,
+               "host": {"cpus_usable": len(os.sched_getaffinity(0)), "cpus_total": os.cpu_count(),
+                        "rank0_bound_to_gpu_numa_cpus": (f"{bound_cpus[0]}-{bound_cpus[-1]} ({len(bound_cpus)})" if bound_cpus else None)},
                "kernel_timing_pass_ms_per_step": round(ms_prof / args.steps, 3) if ms_prof else None}
         if args.impl == "reference":
             out["impl"] = "reference"

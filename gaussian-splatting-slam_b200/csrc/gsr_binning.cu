@@ -4,7 +4,9 @@
 //
 // Order of the final point list (must equal the reference's stable 64-bit sort):
 //   by tile id, then by depth bits, then by Gaussian id.
-// We get it as: (1) stable sort of Gaussian ids by depth bits (P items, 4 passes);
+// We get it as: (1) stable sort of the VISIBLE Gaussians' ids by depth bits (culled ones carry the key 0xFFFFFFFF and
+//                   are dropped by the sort's first pass, so 3 of the 4 passes, the scan and the emission run over
+//                   the visible count only -- half of P on the bench scene; that count stays on the device);
 //               (2) emit instances walking the Gaussians in that order (offsets from a scan taken in
 //                   the same order);  (3) stable sort of instances by tile id only.
 #include "gsr_common.cuh"
@@ -44,14 +46,20 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* w
 // status[0..m) = tile words, status[m] = grand total, status[m + 1] = ticket; all zeroed before the launch.
 constexpr uint32_t kScanOwn = 1u << 30, kScanIncl = 2u << 30, kScanVal = (1u << 30) - 1u;
 __global__ void __launch_bounds__(kScanThreads) scan_chained_kernel(const uint32_t* __restrict__ counts,
-                                                                     const uint32_t* __restrict__ order, int n, int m,
+                                                                     const uint32_t* __restrict__ order,
+                                                                     const uint32_t* __restrict__ n_dev, int m_slots,
                                                                      uint32_t* __restrict__ status,
                                                                      uint32_t* __restrict__ out) {
+    // n (items, in depth order) lives on the device; the grid covers the host's upper bound and m_slots only fixes
+    // where the total and the ticket sit. CTAs whose ticket lies beyond the last tile leave at once.
     __shared__ uint32_t warp_sums[kScanThreads / 32];
     __shared__ uint32_t s_tile, s_prefix;
-    if (threadIdx.x == 0) s_tile = atomicAdd(status + m + 1, 1u);
+    if (threadIdx.x == 0) s_tile = atomicAdd(status + m_slots + 1, 1u);
     __syncthreads();
     const int tile = (int)s_tile;
+    const int n = (int)__ldg(n_dev);
+    const int m = (n + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE;
+    if (tile >= m) return;
     const int base = tile * GSR_SCAN_TILE + threadIdx.x * kScanItems;
     uint32_t c[kScanItems], v = 0;
 #pragma unroll
@@ -83,7 +91,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_chained_kernel(const uint32
         }
         if (lane == 0) {
             if (tile > 0) vs[tile] = kScanIncl | (prefix + total);
-            if (tile == m - 1) status[m] = prefix + total;
+            if (tile == m - 1) status[m_slots] = prefix + total;
             s_prefix = prefix;
         }
     }
@@ -100,12 +108,14 @@ int launch_order_and_scan(const gsr_view& v, GeomState& g, uint32_t** total_dev,
     const int P = v.P;
     bool in_a = true;
     GSR_MEMSET("memset_scan", s, g.scan_sums, 0, sizeof(uint32_t) * ((size_t)(P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE + 8));
-    int e = radix_sort_u32(g.dkey, g.order, g.dkey_tmp, g.order_tmp, P, 32, g.sort_scratch, &in_a, v.debug != 0, s);
+    uint32_t* n_vis = nullptr;
+    int e = radix_sort_u32(g.dkey, g.order, g.dkey_tmp, g.order_tmp, P, 32, g.sort_scratch, &in_a, v.debug != 0, s, &n_vis);
     if (e) return e;
-    // 4 passes: the result is back in (dkey, order)
+    // 4 passes: the result is back in (dkey, order); its first *n_vis entries are the visible Gaussians
+    if (n_vis != g.n_visible) return GSR_E_BADARG;              // layout contract between the two files
     const int m = (P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE;
     GSR_LAUNCH("scan_chained", v.debug, s,
-               (scan_chained_kernel<<<m, kScanThreads, 0, s>>>(g.tiles_touched, g.order, P, m, g.scan_sums, g.point_offsets)));
+               (scan_chained_kernel<<<m, kScanThreads, 0, s>>>(g.tiles_touched, g.order, n_vis, m, g.scan_sums, g.point_offsets)));
     *total_dev = g.scan_sums + m;
     return 0;
 }
@@ -124,7 +134,7 @@ __device__ __forceinline__ void rect_of(float px, float py, int max_radius, int 
 // range, so the lanes walk that range 32 slots at a time -- fully coalesced stores -- and find the owner of their
 // slot by a 5-step binary search over the lanes' end offsets (shuffles). Replaces the thread-serial, divergent loop of
 // duplicateWithKeys (rasterizer_impl.cu:88-109): a warp-store there touches 32 different sectors.
-__global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint32_t* __restrict__ order,
+__global__ void __launch_bounds__(256) emit_instances_kernel(const uint32_t* __restrict__ n_dev, const uint32_t* __restrict__ order,
                                                               const uint32_t* __restrict__ tiles_touched,
                                                               const uint32_t* __restrict__ offsets,
                                                               const float4* __restrict__ rec,
@@ -133,6 +143,8 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint32
                                                               uint32_t* __restrict__ vals) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
+    const int P = (int)__ldg(n_dev);               // visible Gaussians (depth order); the grid covers the host's bound
+    if (j - lane >= P) return;
     uint32_t g = 0, n = 0, end = 0;
     int x0 = 0, y0 = 0, bw = 1;
     if (j < P) {
@@ -146,7 +158,6 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint32
             bw = x1 - x0;
         }
     }
-    // culled Gaussians sort to the end (key 0xFFFFFFFF): whole warps of them leave here
     if (__ballot_sync(0xffffffffu, n > 0) == 0u) return;
     // lanes beyond P: end = end of the last valid lane so the search never selects them
     const uint32_t last_end = __shfl_sync(0xffffffffu, end, min(31, P - 1 - (j - lane)));
@@ -221,7 +232,7 @@ int launch_binning(const gsr_view& v, const GeomState& g, const int* radii, Binn
     uint32_t *ka = b.tile_keys, *va = b.point_list, *kb = b.tile_keys_tmp, *vb = b.vals_tmp;
     if (passes % 2) { ka = b.tile_keys_tmp; va = b.vals_tmp; kb = b.tile_keys; vb = b.point_list; }
     GSR_LAUNCH("emit_instances", v.debug, s,
-               (emit_instances_kernel<<<(v.P + 255) / 256, 256, 0, s>>>(v.P, g.order, g.tiles_touched, g.point_offsets,
+               (emit_instances_kernel<<<(v.P + 255) / 256, 256, 0, s>>>(g.n_visible, g.order, g.tiles_touched, g.point_offsets,
                                                                         g.rec, radii, gx, gy, ka, va)));
     bool in_a = true;
     int e = radix_sort_u32(ka, va, kb, vb, R, tbits, b.sort_scratch, &in_a, v.debug != 0, s);

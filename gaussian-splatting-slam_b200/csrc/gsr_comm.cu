@@ -21,7 +21,8 @@
 namespace gsr {
 
 constexpr int kCommThreads = 512;
-constexpr int kCommUnroll = 4;          // 16-byte requests in flight per thread and peer
+constexpr int kCommUnroll = 4;          // 16-byte requests in flight per thread and peer (peer variant)
+constexpr int kCommUnrollMc = 8;        // multicast variant: one request covers all peers, registers allow more in flight
 
 struct CommArgs {
     float4* buf[GSR_COMM_MAX_PEERS];
@@ -79,14 +80,15 @@ __global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_kernel(const __
     twin_barrier(a);
     const long long stride = (long long)gridDim.x * kCommThreads;
     const int world = WORLD > 0 ? WORLD : a.world;
-    for (long long i0 = a.lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < a.hi; i0 += stride * kCommUnroll) {
-        float4 v[kCommUnroll];
+    constexpr int U = MULTICAST ? kCommUnrollMc : kCommUnroll;
+    for (long long i0 = a.lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < a.hi; i0 += stride * U) {
+        float4 v[U];
         if (MULTICAST) {
 #pragma unroll
-            for (int u = 0; u < kCommUnroll; u++)
+            for (int u = 0; u < U; u++)
                 if (i0 + u * stride < a.hi) v[u] = mc_ld_reduce(a.mc + i0 + u * stride);
 #pragma unroll
-            for (int u = 0; u < kCommUnroll; u++)
+            for (int u = 0; u < U; u++)
                 if (i0 + u * stride < a.hi) mc_st(a.mc + i0 + u * stride, v[u]);
         } else {
             float4 w[kCommUnroll];

@@ -64,6 +64,7 @@ struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46
     uint32_t* point_offsets;  // [P] inclusive scan of tiles_touched[order[j]]  (depth order!)
     uint32_t* scan_sums;      // [scan tiles + 8]; last word = total (num_rendered)
     uint32_t* sort_scratch;   // radix-sort tables for the P-sized sort
+    uint32_t* n_visible;      // [1] Gaussians that survived the cull = valid prefix of order / point_offsets (device)
     static GeomState from(char*& p, size_t P) {
         GeomState g;
         g.depths = carve<float>(p, P);
@@ -77,6 +78,7 @@ struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46
         g.point_offsets = carve<uint32_t>(p, P);
         g.scan_sums = carve<uint32_t>(p, (P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE + 8);
         g.sort_scratch = carve<uint32_t>(p, sort_scratch_words(P));
+        g.n_visible = g.sort_scratch + 4 * GSR_RADIX + 8;      // where radix_sort_u32's drop mode leaves the kept count
         return g;
     }
 };
@@ -144,7 +146,7 @@ int launch_preprocess_backward(const gsr_view& v, const GeomState& g, const int*
 // Stable LSD radix sort of (u32 key, u32 value) pairs on key bits [0, total_bits). Ping-pongs between
 // (ka,va) and (kb,vb); *result_in_a tells where the sorted data ended up. scratch: sort_scratch_words(n).
 int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits,
-                   uint32_t* scratch, bool* result_in_a, bool debug, cudaStream_t s);
+                   uint32_t* scratch, bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev = nullptr);
 static inline int radix_passes(int total_bits) { return (total_bits + 7) / 8; }
 int launch_sorted_keys_debug(const gsr_view& v, const GeomState& g, const BinningState& b, int R, uint64_t* keys_out,
                              cudaStream_t s);

@@ -70,7 +70,7 @@ __device__ __forceinline__ uint32_t block_excl_scan256(uint32_t v, uint32_t* war
 
 // ------------------------------------------------------------------ digit histograms of every pass, one read of the keys
 __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const uint32_t* __restrict__ keys, int n, int passes,
-                                                                   int total_bits, uint32_t* __restrict__ ghist) {
+                                                                   int total_bits, uint32_t* __restrict__ ghist, int drop) {
     // kHistCopies replicas per digit, picked by lane: depth exponents put most keys of a warp into a few digits of
     // the top byte, and same-address shared atomics serialise (MATCH.ANY aggregation measured slower than this)
     __shared__ uint32_t sh[4][kHistCopies][GSR_RADIX];
@@ -85,6 +85,7 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const uint32_t
         const uint32_t kk[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int j = 0; j < 4; j++) {
+            if (drop && kk[j] == 0xFFFFFFFFu) continue;            // dropped keys are in no histogram
             for (int p = 0; p < passes; p++) {
                 const int bits = min(8, total_bits - 8 * p);
                 atomicAdd(&sh[p][cp][(kk[j] >> (8 * p)) & ((1u << bits) - 1u)], 1u);
@@ -93,7 +94,7 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const uint32_t
     }
     if (blockIdx.x == 0 && t < (n & 3)) {                          // tail (< 4 keys)
         const uint32_t k = __ldg(keys + (nvec << 2) + t);
-        for (int p = 0; p < passes; p++) {
+        for (int p = 0; p < (drop && k == 0xFFFFFFFFu ? 0 : passes); p++) {
             const int bits = min(8, total_bits - 8 * p);
             atomicAdd(&sh[p][0][(k >> (8 * p)) & ((1u << bits) - 1u)], 1u);
         }
@@ -120,6 +121,7 @@ struct SortSmem {
     uint32_t gofs[GSR_RADIX];                // global start of the digit's run minus its local start
     uint32_t warp_sums[kSortWarps];
     uint32_t tile, next;
+    uint32_t n_valid, count_out;             // drop mode: keys that survive (whole sort / this tile)
 };
 
 __device__ __forceinline__ void sort_cp16(void* smem, const void* gmem) {
@@ -151,7 +153,7 @@ __device__ __forceinline__ void sort_prefetch(SortSmem& sm, const uint32_t* __re
 }
 
 // ranks, publishes, reorders and writes out one tile whose pairs are already in registers
-template <int BITS, bool FULL>
+template <int BITS, bool FULL, bool DROP>
 __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key)[kSortItems], const uint32_t (&val)[kSortItems],
                                               uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n,
                                               int shift, int tile, uint32_t gbase, uint32_t* __restrict__ status) {
@@ -165,9 +167,9 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
     const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        const bool ok = FULL || wofs + i * 32 < count;
+        const bool ok = (FULL || wofs + i * 32 < count) && (!DROP || key[i] != 0xFFFFFFFFu);
         const uint32_t d = (key[i] >> shift) & mask;
-        const uint32_t peers = same_digit_lanes<BITS>(d, FULL ? kAll : __ballot_sync(kAll, ok));
+        const uint32_t peers = same_digit_lanes<BITS>(d, (FULL && !DROP) ? kAll : __ballot_sync(kAll, ok));
         const int leader = __ffs(peers) - 1;                       // invalid lanes: garbage, never used
         uint32_t prev = 0;
         if (ok && lane == leader) prev = atomicAdd(&sm.whist[w][d], (uint32_t)__popc(peers));   // same warp: program order
@@ -182,6 +184,7 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
     uint32_t* my_status = status + (size_t)tile * GSR_RADIX + t;
     st_relaxed(my_status, (tile == 0 ? kFlagInc : kFlagAgg) | run);            // publish early: successors can proceed
     const uint32_t ds = block_excl_scan256(run, sm.warp_sums);
+    if (DROP && t == kSortThreads - 1) sm.count_out = ds + run;                // pairs of this tile that are kept
     uint32_t acc = ds;
 #pragma unroll
     for (int k = 0; k < kSortWarps; k++) { sm.whist[k][t] = acc; acc += cnt[k]; }
@@ -189,7 +192,7 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
     // reorder inside shared memory
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
-        if (FULL || wofs + i * 32 < count) {
+        if ((FULL || wofs + i * 32 < count) && (!DROP || key[i] != 0xFFFFFFFFu)) {
             const uint32_t lp = sm.whist[w][(key[i] >> shift) & mask] + rank[i];
             sm.s_keys[lp] = key[i];
             sm.s_vals[lp] = val[i];
@@ -224,10 +227,11 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
     sm.gofs[t] = gbase + excl - ds;
     __syncthreads();
     // coalesced runs out
+    const int count_out = DROP ? (int)sm.count_out : count;
 #pragma unroll
     for (int i = 0; i < kSortItems; i++) {
         const int slot = i * kSortThreads + t;
-        if (FULL || slot < count) {
+        if ((FULL && !DROP) || slot < count_out) {
             const uint32_t k = sm.s_keys[slot];
             const uint32_t pos = sm.gofs[(k >> shift) & mask] + (uint32_t)slot;
             keys_out[pos] = k;
@@ -236,20 +240,34 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
     }
 }
 
-template <int BITS>
+// MODE 0: plain pass. MODE 1 ("drop"): pairs whose key is 0xFFFFFFFF are left out of the output (the histograms do not
+// count them either), so the pass also compacts; the number of kept pairs goes to *n_valid_out. MODE 2: a pass after a
+// drop pass -- the pair count is not known to the host, it is the total of this pass's own histogram.
+template <int BITS, int MODE>
 __global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_t* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     uint32_t* __restrict__ keys_out,
                                                                     uint32_t* __restrict__ vals_out, int n, int n_tiles,
                                                                     int shift, const uint32_t* __restrict__ ghist,
                                                                     uint32_t* __restrict__ ticket,
-                                                                    uint32_t* __restrict__ status) {
+                                                                    uint32_t* __restrict__ status,
+                                                                    uint32_t* __restrict__ n_valid_out) {
     extern __shared__ __align__(16) unsigned char sort_smem_raw[];
     SortSmem& sm = *reinterpret_cast<SortSmem*>(sort_smem_raw);
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     if (t == 0) sm.tile = atomicAdd(ticket, 1u);
-    const uint32_t gbase = block_excl_scan256(__ldg(ghist + t), sm.warp_sums);   // first output slot of digit t (syncs)
+    const uint32_t hcount = __ldg(ghist + t);
+    const uint32_t gbase = block_excl_scan256(hcount, sm.warp_sums);   // first output slot of digit t (syncs)
+    if (MODE != 0) {
+        if (t == kSortThreads - 1) sm.n_valid = gbase + hcount;
+        __syncthreads();
+        if (MODE == 2) {
+            n = (int)sm.n_valid;
+            n_tiles = (n + GSR_SORT_TILE - 1) / GSR_SORT_TILE;
+        }
+    }
     int tile = (int)sm.tile;
+    if (MODE == 1 && tile == 0 && t == 0) *n_valid_out = sm.n_valid;
     if (tile >= n_tiles) return;
     sort_prefetch(sm, keys_in, vals_in, n, tile);
     const int wofs = w * (32 * kSortItems) + lane;
@@ -266,32 +284,39 @@ __global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_
         __syncthreads();                                   // everybody holds its pairs: the prefetch buffers are free again
         if (next < n_tiles) sort_prefetch(sm, keys_in, vals_in, n, next);
         if ((tile + 1) * GSR_SORT_TILE <= n)
-            onesweep_tile<BITS, true>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
+            onesweep_tile<BITS, true, MODE == 1>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
         else
-            onesweep_tile<BITS, false>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
+            onesweep_tile<BITS, false, MODE == 1>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
         if (next >= n_tiles) break;
         tile = next;
         __syncthreads();                                   // reorder buffers / gofs are read until here
     }
 }
 
-template <int BITS>
+template <int BITS, int MODE = 0>
 static int launch_pass(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, int n, int shift,
-                       const uint32_t* ghist, uint32_t* ticket, uint32_t* status, int tiles, cudaStream_t s) {
+                       const uint32_t* ghist, uint32_t* ticket, uint32_t* status, int tiles, cudaStream_t s,
+                       uint32_t* n_valid_out = nullptr) {
     static bool attr_set = false;                          // one process drives one device
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(onesweep_kernel<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
+        cudaError_t e = cudaFuncSetAttribute(onesweep_kernel<BITS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
     const int ctas = tiles < 148 * 3 ? tiles : 148 * 3;
-    onesweep_kernel<BITS><<<ctas, kSortThreads, sizeof(SortSmem), s>>>(kin, vin, kout, vout, n, tiles, shift, ghist, ticket, status);
+    onesweep_kernel<BITS, MODE><<<ctas, kSortThreads, sizeof(SortSmem), s>>>(kin, vin, kout, vout, n, tiles, shift, ghist, ticket, status, n_valid_out);
     return 0;
 }
 
 int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits, uint32_t* scratch,
-                   bool* result_in_a, bool debug, cudaStream_t s) {
+                   bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev) {
+    // n_valid_dev != NULL ("drop" sort, 32-bit keys only): pairs whose key is 0xFFFFFFFF are not part of the result;
+    // the first pass compacts them away, the later passes run over the kept pairs only, and *n_valid_dev points at
+    // their count (device). The tail of the output arrays beyond that count is unspecified.
+    const bool drop = n_valid_dev != nullptr;
+    if (drop && total_bits != 32) return GSR_E_BADARG;
     *result_in_a = true;
+    if (drop) *n_valid_dev = scratch + 4 * GSR_RADIX + 8;          // a spare word of the ticket block (zeroed below)
     if (n <= 0 || total_bits <= 0) return 0;
     const int passes = radix_passes(total_bits);
     const int tiles = (int)sort_tiles((size_t)n);
@@ -301,7 +326,7 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
     GSR_MEMSET("memset_sort", s, scratch, 0, sizeof(uint32_t) * (4 * GSR_RADIX + 64 + (size_t)passes * tiles * GSR_RADIX));
     const int hist_blocks = min((n / 4 + kSortThreads - 1) / kSortThreads, 148 * 8);
     GSR_LAUNCH("radix_hist", debug, s,
-               (radix_hist_kernel<<<hist_blocks > 0 ? hist_blocks : 1, kSortThreads, 0, s>>>(ka, n, passes, total_bits, ghist)));
+               (radix_hist_kernel<<<hist_blocks > 0 ? hist_blocks : 1, kSortThreads, 0, s>>>(ka, n, passes, total_bits, ghist, drop ? 1 : 0)));
     uint32_t *kin = ka, *vin = va, *kout = kb, *vout = vb;
     for (int p = 0; p < passes; p++) {
         const int shift = 8 * p;
@@ -310,7 +335,9 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
         const uint32_t* gh = ghist + p * GSR_RADIX;
         int le = 0;
         GSR_LAUNCH("onesweep_pass", debug, s, {
-            switch (bits) {
+            if (drop && p == 0) le = launch_pass<8, 1>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s, *n_valid_dev);
+            else if (drop) le = launch_pass<8, 2>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s);
+            else switch (bits) {
                 case 1: le = launch_pass<1>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
                 case 2: le = launch_pass<2>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
                 case 3: le = launch_pass<3>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;

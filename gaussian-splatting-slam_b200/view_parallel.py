@@ -89,6 +89,11 @@ class PeerExchange:
         for p in range(h.world_size):
             g.buf[p] = int(h.buffer_ptrs[p]) + off
             g.signal[p] = int(sh.buffer_ptrs[p]) + soff
+        # link bytes per rank and direction for a bucket of S bytes: multicast (world + 1) / world x S (the switch also
+        # pulls the local contribution), peer loads + stores 2 (world - 1) / world x S -- multicast wins from 4 ranks on
+        # (measured at 2 ranks, 708 MB: peer 1.06 ms, multicast 1.83 ms, NCCL 1.31 ms; profiles/r01e_comm_check_n2.json)
+        if multicast == "auto":
+            multicast = h.world_size >= 4
         mc = int(h.multicast_ptr) if multicast else 0
         g.multicast = (mc + off) if mc else None
         self.desc, self.numel, self.has_multicast = g, numel, bool(mc)
@@ -96,6 +101,27 @@ class PeerExchange:
 
     def all_reduce(self, max_ctas: int = 0):
         peer_all_reduce(self.desc, self.numel, max_ctas)
+
+
+def bind_rank_to_gpu_numa(device_index: int):
+    """Pins the calling process to the CPUs NVML reports as local to GPU `device_index` (its NUMA node), so that the
+    rank's pinned host buffers are first-touched next to its GPU and its H2D / D2H copies do not cross the socket
+    interconnect. With 8 ranks sharing one host this is what keeps the end-to-end (host-buffer) path scaling.
+    Returns the CPU list it bound to, or None when NVML has no answer (the process then stays as it was)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:       # noqa: BLE001 - no NVML / no permission: leave the affinity alone
+        return None
 
 
 def shard_views(num_views: int, rank: int, world_size: int) -> List[int]:
@@ -142,7 +168,7 @@ class GradBucket:
         """Sets the peer-memory exchange up on all ranks or on none (the ranks agree through a MIN all-reduce)."""
         px, err = None, None
         try:
-            px = PeerExchange(numel, self.device, group, multicast=(mode != "peer"))
+            px = PeerExchange(numel, self.device, group, multicast={"peer": False, "multimem": True}.get(mode, "auto"))
             if mode == "multimem" and not px.has_multicast:
                 raise RuntimeError("no NVSwitch multicast mapping for the bucket")
         except Exception as e:          # noqa: BLE001 - any set-up failure means "not available here"

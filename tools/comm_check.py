@@ -83,7 +83,8 @@ def main():
         identical_across_ranks = torch.tensor([int(torch.equal(same, px.flat))], device=dev)
         dist.all_reduce(identical_across_ranks, op=dist.ReduceOp.MIN)
         med, best = time_it(px.all_reduce)
-        per_rank_link_bytes = numel * 4 * (world - 1) / world
+        # bytes through one rank's links, per direction (see view_parallel.PeerExchange)
+        per_rank_link_bytes = numel * 4 * ((world + 1) / world if kind == "multimem" else 2 * (world - 1) / world)
         out["paths"][kind] = {"available": True, "max_abs_diff": float(diff), "rel_l2": rel, "bit_exact_vs_rank_order": bit_exact,
                               "identical_on_all_ranks": bool(identical_across_ranks.item()), "ms_median": med, "ms_best": best,
                               "link_GBps_per_rank_per_dir": per_rank_link_bytes / med / 1e6}
@@ -94,7 +95,7 @@ def main():
     rel = float((flat - want).double().norm() / want.double().norm())
     med, best = time_it(lambda: dist.all_reduce(flat))
     out["paths"]["nccl"] = {"available": True, "rel_l2": rel, "ms_median": med, "ms_best": best,
-                            "link_GBps_per_rank_per_dir": numel * 4 * (world - 1) / world / med / 1e6}
+                            "link_GBps_per_rank_per_dir": numel * 4 * 2 * (world - 1) / world / med / 1e6}
     if rank == 0:
         line = json.dumps(out)
         print(line)
