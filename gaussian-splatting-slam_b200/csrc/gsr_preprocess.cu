@@ -173,6 +173,8 @@ __device__ __forceinline__ V3 sh_color(int idx, int deg, int max_coeffs, V3 pos,
     return {fmaxf(result.x, 0.0f), fmaxf(result.y, 0.0f), fmaxf(result.z, 0.0f)};
 }
 
+__device__ __forceinline__ void pre_prefetch_l2(const void* gmem) { asm volatile("prefetch.global.L2 [%0];" ::"l"(gmem)); }
+
 struct PreArgs {
     int P, D, M, W, H;
     float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
@@ -195,6 +197,15 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
     const dim3 grid((a.W + GSR_TILE - 1) / GSR_TILE, (a.H + GSR_TILE - 1) / GSR_TILE, 1);
     do {
         const float3 p_orig = {__ldg(a.means3D + 3 * idx), __ldg(a.means3D + 3 * idx + 1), __ldg(a.means3D + 3 * idx + 2)};
+        // The covariance inputs are requested together with the position, before the cull is known: the arrays are dense,
+        // so with half the Gaussians visible nearly every sector is fetched anyway, and the cull no longer sits between
+        // two dependent memory round trips.
+        V3 sc = {0.f, 0.f, 0.f};
+        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.cov3D_precomp == nullptr) {
+            sc = V3{__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2)};
+            q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+        }
         const float3 p_view = xform43(p_orig, a.view);
         if (p_view.z <= 0.2f) {                                  // auxiliary.h:154
             if (a.prefiltered) {
@@ -206,13 +217,18 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
         const float4 p_hom = xform44(p_orig, a.proj);
         const float p_w = 1.0f / (p_hom.w + 0.0000001f);
         const float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+        // A centre that projects near the screen almost always survives the rectangle test below: pull its SH row
+        // (192 bytes, two lines) into L2 now, while the covariance is computed. A hint only -- a large splat centred
+        // far outside just reads its row from DRAM as before.
+        if (SH16 && fabsf(p_proj.x) < 1.25f && fabsf(p_proj.y) < 1.25f) {
+            pre_prefetch_l2(a.shs + (size_t)idx * 48);
+            pre_prefetch_l2(a.shs + (size_t)idx * 48 + 32);
+        }
         float c3[6];
         if (a.cov3D_precomp != nullptr) {
 #pragma unroll
             for (int k = 0; k < 6; k++) c3[k] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + k);
         } else {
-            const V3 sc = {__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2)};
-            const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
             cov3d_of(sc, a.scale_modifier, q, c3);
         }
         float3 cov = cov2d_of(p_orig, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, c3, a.view);
@@ -320,7 +336,21 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
     const bool inside = idx < a.P;
     if (!SH16 && !inside) return;                     // the SH16 path has CTA-wide barriers: everybody stays
     const gsr_grads& o = b.out;
-    const bool vis = inside && b.radii[idx] > 0;
+    // position, scale and rotation are requested together with the radius that decides visibility (dense arrays: with
+    // half the Gaussians visible nearly every sector is needed anyway), so they do not wait for that decision
+    float3 mean = {0.f, 0.f, 0.f};
+    float sc[3] = {0.f, 0.f, 0.f};
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+    int my_radius = 0;
+    if (inside) {
+        my_radius = b.radii[idx];
+        mean = make_float3(__ldg(a.means3D + 3 * idx), __ldg(a.means3D + 3 * idx + 1), __ldg(a.means3D + 3 * idx + 2));
+        if (a.cov3D_precomp == nullptr) {
+            sc[0] = __ldg(a.scales + 3 * idx); sc[1] = __ldg(a.scales + 3 * idx + 1); sc[2] = __ldg(a.scales + 3 * idx + 2);
+            q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+        }
+    }
+    const bool vis = my_radius > 0;
     const int M = a.M;
     // SH16 path: the coefficient rows of the CTA's visible Gaussians are fetched COOPERATIVELY -- consecutive threads take
     // consecutive 16-byte pieces, so one warp-wide request covers 4 lines instead of the 32 a row-per-thread access
@@ -346,14 +376,25 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
         if (vis) s_owner[slot] = (uint8_t)threadIdx.x;
         __syncthreads();
         const float* src0 = a.shs + (size_t)blockIdx.x * 256 * 48;
+        const bool rmw = o.accumulate != 0;
+        const float* grad0 = o.dL_dsh + (size_t)blockIdx.x * 256 * 48;
         for (int f = threadIdx.x; f < n_vis * n_quads; f += 256) {
             const int sl = f / n_quads, k = f - sl * n_quads;
-            pre_cp_async16(s_rows + sl * kShRow + 4 * k, src0 + (size_t)s_owner[sl] * 48 + 4 * k);
+            const size_t at = (size_t)s_owner[sl] * 48 + 4 * k;
+            pre_cp_async16(s_rows + sl * kShRow + 4 * k, src0 + at);
+            // accumulate mode reads the gradient rows back at the very end: pull them into L2 now (one request per
+            // 128 bytes of the row), so that those reads do not pay a DRAM round trip each
+            if (rmw && (k & 7) == 0) pre_prefetch_l2(grad0 + at);
         }
         pre_cp_async_commit();
     }
+    if (vis && o.accumulate != 0) {                    // same for the small per-Gaussian gradients
+        pre_prefetch_l2(o.dL_dopacity + idx);
+        pre_prefetch_l2(o.dL_dmeans3D + 3 * (size_t)idx);
+        if (o.dL_dscales) pre_prefetch_l2(o.dL_dscales + 3 * (size_t)idx);
+        if (o.dL_drotations) pre_prefetch_l2(o.dL_drotations + 4 * (size_t)idx);
+    }
     float4* const my_row = reinterpret_cast<float4*>(s_rows + slot * kShRow);
-    float3 mean = {0.f, 0.f, 0.f};
 
     float dmean[3] = {0.f, 0.f, 0.f}, dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float dmean2d[2] = {0.f, 0.f}, dopac = 0.f, dcolor[3] = {0.f, 0.f, 0.f}, dconic[3] = {0.f, 0.f, 0.f};
@@ -372,18 +413,13 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
         dcolor[0] = a1.z; dcolor[1] = a1.w; dcolor[2] = a2.x;
         const float dinvd = b.have_invdepth ? a2.y : 0.f;
 
-        mean = make_float3(__ldg(a.means3D + 3 * idx), __ldg(a.means3D + 3 * idx + 1), __ldg(a.means3D + 3 * idx + 2));
         const float* view = a.view;
         const float* proj = a.proj;
         float c3[6];
-        float4 q = make_float4(0, 0, 0, 0);
-        float sc[3] = {0, 0, 0};
         if (a.cov3D_precomp != nullptr) {
 #pragma unroll
             for (int k = 0; k < 6; k++) c3[k] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + k);
         } else {
-            sc[0] = __ldg(a.scales + 3 * idx); sc[1] = __ldg(a.scales + 3 * idx + 1); sc[2] = __ldg(a.scales + 3 * idx + 2);
-            q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
             cov3d_of(V3{sc[0], sc[1], sc[2]}, a.scale_modifier, q, c3);
         }
         // ---- recompute the projection (backward.cu:158-200)
@@ -589,27 +625,49 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
             reinterpret_cast<float4*>(o.dL_dconic)[idx] = make_float4(dconic[0], dconic[1], 0.f, dconic[2]);
     }
     if (inside && !(accum && !vis)) {
-        auto put = [accum](float* p, float v) { *p = accum ? *p + v : v; };
-        auto put4 = [accum](float4* p, float4 v) {
-            if (accum) { const float4 c = *p; v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w; }
-            *p = v;
-        };
-        put(o.dL_dopacity + idx, dopac);
+        // accumulate mode: every old value is loaded BEFORE the first store. Written one after the other (load, add,
+        // store, next) the stores keep the later loads behind them -- the pointers may alias as far as the compiler
+        // knows -- and a thread pays one memory round trip per output array.
+        float old_op = 0.f, old_m[3] = {0.f, 0.f, 0.f}, old_c[3] = {0.f, 0.f, 0.f}, old_v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        float old_s[3] = {0.f, 0.f, 0.f};
+        float4 old_r = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (accum) {
+            old_op = o.dL_dopacity[idx];
 #pragma unroll
-        for (int k = 0; k < 3; k++) put(o.dL_dmeans3D + 3 * (size_t)idx + k, dmean[k]);
+            for (int k = 0; k < 3; k++) old_m[k] = o.dL_dmeans3D[3 * (size_t)idx + k];
+            if (o.dL_dcolors) {
+#pragma unroll
+                for (int k = 0; k < 3; k++) old_c[k] = o.dL_dcolors[3 * (size_t)idx + k];
+            }
+            if (o.dL_dcov3D) {
+#pragma unroll
+                for (int k = 0; k < 6; k++) old_v[k] = o.dL_dcov3D[6 * (size_t)idx + k];
+            }
+            if (o.dL_dscales) {
+#pragma unroll
+                for (int k = 0; k < 3; k++) old_s[k] = o.dL_dscales[3 * (size_t)idx + k];
+            }
+            if (o.dL_drotations) old_r = reinterpret_cast<const float4*>(o.dL_drotations)[idx];
+        }
+        auto put = [accum](float* p, float v) { *p = accum ? *p + v : v; };      // (SH fallback path below)
+        o.dL_dopacity[idx] = old_op + dopac;
+#pragma unroll
+        for (int k = 0; k < 3; k++) o.dL_dmeans3D[3 * (size_t)idx + k] = old_m[k] + dmean[k];
         if (o.dL_dcolors) {
 #pragma unroll
-            for (int k = 0; k < 3; k++) put(o.dL_dcolors + 3 * (size_t)idx + k, dcolor[k]);
+            for (int k = 0; k < 3; k++) o.dL_dcolors[3 * (size_t)idx + k] = old_c[k] + dcolor[k];
         }
         if (o.dL_dcov3D) {
 #pragma unroll
-            for (int k = 0; k < 6; k++) put(o.dL_dcov3D + 6 * (size_t)idx + k, dcov[k]);
+            for (int k = 0; k < 6; k++) o.dL_dcov3D[6 * (size_t)idx + k] = old_v[k] + dcov[k];
         }
         if (o.dL_dscales) {
 #pragma unroll
-            for (int k = 0; k < 3; k++) put(o.dL_dscales + 3 * (size_t)idx + k, dscale[k]);
+            for (int k = 0; k < 3; k++) o.dL_dscales[3 * (size_t)idx + k] = old_s[k] + dscale[k];
         }
-        if (o.dL_drotations) put4(reinterpret_cast<float4*>(o.dL_drotations) + idx, make_float4(drot[0], drot[1], drot[2], drot[3]));
+        if (o.dL_drotations)
+            reinterpret_cast<float4*>(o.dL_drotations)[idx] =
+                make_float4(old_r.x + drot[0], old_r.y + drot[1], old_r.z + drot[2], old_r.w + drot[3]);
         if (o.dL_dsh || o.dL_ddc) {
             if (SH16) {
                 if (vis) {
@@ -642,12 +700,27 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
         // coefficients above the active degree have zero gradient: in accumulate mode they need no traffic at all
         const int nq = accum ? n_quads : 12;
         float* dst0 = o.dL_dsh + (size_t)blockIdx.x * 256 * 48;
-        for (int f = threadIdx.x; f < n_vis * nq; f += 256) {
-            const int sl = f / nq, k = f - sl * nq;
-            float4 v = *reinterpret_cast<const float4*>(s_rows + sl * kShRow + 4 * k);
-            float4* d = reinterpret_cast<float4*>(dst0 + (size_t)s_owner[sl] * 48 + 4 * k);
-            if (accum) { const float4 c = *d; v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w; }
-            *d = v;
+        const int total = n_vis * nq;
+        constexpr int kU = 4;                          // old rows: kU 16-byte loads in flight per thread before any store
+        for (int f0 = threadIdx.x; f0 < total; f0 += 256 * kU) {
+            float4* d[kU];
+            float4 c[kU], v[kU];
+#pragma unroll
+            for (int u = 0; u < kU; u++) {
+                const int f = f0 + 256 * u;
+                c[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (f < total) {
+                    const int sl = f / nq, k = f - sl * nq;
+                    d[u] = reinterpret_cast<float4*>(dst0 + (size_t)s_owner[sl] * 48 + 4 * k);
+                    v[u] = *reinterpret_cast<const float4*>(s_rows + sl * kShRow + 4 * k);
+                    if (accum) c[u] = *d[u];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < kU; u++) {
+                if (f0 + 256 * u < total)
+                    *d[u] = make_float4(v[u].x + c[u].x, v[u].y + c[u].y, v[u].z + c[u].z, v[u].w + c[u].w);
+            }
         }
     }
 }
