@@ -146,7 +146,7 @@ int gsr_geom_layout(int P, size_t* off, int max_off) {
     char* p = nullptr;
     GeomState g = GeomState::from(p, (size_t)P);
     const size_t v[] = {(size_t)g.depths, (size_t)g.rec, (size_t)g.clamped, (size_t)g.tiles_touched,
-                        (size_t)g.point_offsets, (size_t)g.order, (size_t)g.dkey};
+                        (size_t)g.point_offsets, (size_t)g.order, (size_t)g.dkey, (size_t)g.rect_packed};
     int n = 0;
     for (; n < (int)(sizeof(v) / sizeof(v[0])) && n < max_off; n++) off[n] = v[n];
     return n;

@@ -45,11 +45,15 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* w
 // Tiles are taken by ticket, which makes waiting on lower-numbered tiles safe whatever the CTA scheduling order.
 // status[0..m) = tile words, status[m] = grand total, status[m + 1] = ticket; all zeroed before the launch.
 constexpr uint32_t kScanOwn = 1u << 30, kScanIncl = 2u << 30, kScanVal = (1u << 30) - 1u;
+// PACKED: `counts` holds packed tile rectangles (GeomState::rect_packed); the count is width x height and the word is
+// also written out in depth order (rect_sorted), so the emission streams it instead of gathering record + radius.
+template <bool PACKED>
 __global__ void __launch_bounds__(kScanThreads) scan_chained_kernel(const uint32_t* __restrict__ counts,
                                                                      const uint32_t* __restrict__ order,
                                                                      const uint32_t* __restrict__ n_dev, int m_slots,
                                                                      uint32_t* __restrict__ status,
-                                                                     uint32_t* __restrict__ out) {
+                                                                     uint32_t* __restrict__ out,
+                                                                     uint32_t* __restrict__ rect_sorted) {
     // n (items, in depth order) lives on the device; the grid covers the host's upper bound and m_slots only fixes
     // where the total and the ticket sit. CTAs whose ticket lies beyond the last tile leave at once.
     __shared__ uint32_t warp_sums[kScanThreads / 32];
@@ -65,6 +69,10 @@ __global__ void __launch_bounds__(kScanThreads) scan_chained_kernel(const uint32
 #pragma unroll
     for (int i = 0; i < kScanItems; i++) {
         c[i] = (base + i < n) ? __ldg(counts + __ldg(order + base + i)) : 0u;
+        if (PACKED) {
+            if (base + i < n) rect_sorted[base + i] = c[i];
+            c[i] = ((c[i] >> 16) & 255u) * (c[i] >> 24);
+        }
         v += c[i];
     }
     uint32_t total;
@@ -104,6 +112,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_chained_kernel(const uint32
     }
 }
 
+
 int launch_order_and_scan(const gsr_view& v, GeomState& g, uint32_t** total_dev, cudaStream_t s) {
     const int P = v.P;
     bool in_a = true;
@@ -114,8 +123,12 @@ int launch_order_and_scan(const gsr_view& v, GeomState& g, uint32_t** total_dev,
     // 4 passes: the result is back in (dkey, order); its first *n_vis entries are the visible Gaussians
     if (n_vis != g.n_visible) return GSR_E_BADARG;              // layout contract between the two files
     const int m = (P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE;
-    GSR_LAUNCH("scan_chained", v.debug, s,
-               (scan_chained_kernel<<<m, kScanThreads, 0, s>>>(g.tiles_touched, g.order, n_vis, m, g.scan_sums, g.point_offsets)));
+    if (rect_packing_ok(v.W, v.H))
+        GSR_LAUNCH("scan_chained", v.debug, s,
+                   (scan_chained_kernel<true><<<m, kScanThreads, 0, s>>>(g.rect_packed, g.order, n_vis, m, g.scan_sums, g.point_offsets, g.rect_sorted)));
+    else
+        GSR_LAUNCH("scan_chained", v.debug, s,
+                   (scan_chained_kernel<false><<<m, kScanThreads, 0, s>>>(g.tiles_touched, g.order, n_vis, m, g.scan_sums, g.point_offsets, nullptr)));
     *total_dev = g.scan_sums + m;
     return 0;
 }
@@ -134,8 +147,9 @@ __device__ __forceinline__ void rect_of(float px, float py, int max_radius, int 
 // range, so the lanes walk that range 32 slots at a time -- fully coalesced stores -- and find the owner of their
 // slot by a 5-step binary search over the lanes' end offsets (shuffles). Replaces the thread-serial, divergent loop of
 // duplicateWithKeys (rasterizer_impl.cu:88-109): a warp-store there touches 32 different sectors.
+template <bool PACKED>
 __global__ void __launch_bounds__(256) emit_instances_kernel(const uint32_t* __restrict__ n_dev, const uint32_t* __restrict__ order,
-                                                              const uint32_t* __restrict__ tiles_touched,
+                                                              const uint32_t* __restrict__ rect_sorted,
                                                               const uint32_t* __restrict__ offsets,
                                                               const float4* __restrict__ rec,
                                                               const int* __restrict__ radii, int gx, int gy,
@@ -151,7 +165,10 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(const uint32_t* __r
         g = __ldg(order + j);
         end = __ldg(offsets + j);                   // inclusive scan in depth order
         n = end - (j > 0 ? __ldg(offsets + j - 1) : 0u);   // = tiles_touched[g], without the gather
-        if (n > 0) {
+        if (PACKED) {                               // streamed, in depth order (written by the scan)
+            const uint32_t r = __ldg(rect_sorted + j);
+            x0 = (int)(r & 255u); y0 = (int)((r >> 8) & 255u); bw = max(1, (int)((r >> 16) & 255u));
+        } else if (n > 0) {
             int x1, y1;
             const float4 r0 = __ldg(rec + 3 * (size_t)g);
             rect_of(r0.x, r0.y, __ldg(radii + g), gx, gy, x0, y0, x1, y1);
@@ -231,9 +248,14 @@ int launch_binning(const gsr_view& v, const GeomState& g, const int* radii, Binn
     // make the sorted result land in (tile_keys, point_list)
     uint32_t *ka = b.tile_keys, *va = b.point_list, *kb = b.tile_keys_tmp, *vb = b.vals_tmp;
     if (passes % 2) { ka = b.tile_keys_tmp; va = b.vals_tmp; kb = b.tile_keys; vb = b.point_list; }
-    GSR_LAUNCH("emit_instances", v.debug, s,
-               (emit_instances_kernel<<<(v.P + 255) / 256, 256, 0, s>>>(g.n_visible, g.order, g.tiles_touched, g.point_offsets,
-                                                                        g.rec, radii, gx, gy, ka, va)));
+    if (rect_packing_ok(v.W, v.H))
+        GSR_LAUNCH("emit_instances", v.debug, s,
+                   (emit_instances_kernel<true><<<(v.P + 255) / 256, 256, 0, s>>>(g.n_visible, g.order, g.rect_sorted, g.point_offsets,
+                                                                              g.rec, radii, gx, gy, ka, va)));
+    else
+        GSR_LAUNCH("emit_instances", v.debug, s,
+                   (emit_instances_kernel<false><<<(v.P + 255) / 256, 256, 0, s>>>(g.n_visible, g.order, nullptr, g.point_offsets,
+                                                                               g.rec, radii, gx, gy, ka, va)));
     bool in_a = true;
     int e = radix_sort_u32(ka, va, kb, vb, R, tbits, b.sort_scratch, &in_a, v.debug != 0, s);
     if (e) return e;

@@ -52,6 +52,12 @@ static inline size_t sort_tiles(size_t n) { return (n + GSR_SORT_TILE - 1) / GSR
 // word per (pass, tile, digit)
 static inline size_t sort_scratch_words(size_t n) { return 4 * GSR_RADIX + 64 + 4 * GSR_RADIX * sort_tiles(n) + 64; }
 
+// packed tile rectangles carry 8 bits per field: images up to 4080 x 4080 pixels; beyond that binning gathers record and
+// radius again and preprocess keeps tiles_touched
+static inline bool rect_packing_ok(int W, int H) {
+    return (W + GSR_TILE - 1) / GSR_TILE <= 255 && (H + GSR_TILE - 1) / GSR_TILE <= 255;
+}
+
 struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46)
     float* depths;            // [P] view-space z (visible Gaussians only)
     float4* rec;              // [3P] splat records: {x,y,ex,ey} {a,b,c,opacity} {r,g,b,1/depth}
@@ -64,6 +70,8 @@ struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46
     uint32_t* point_offsets;  // [P] inclusive scan of tiles_touched[order[j]]  (depth order!)
     uint32_t* scan_sums;      // [scan tiles + 8]; last word = total (num_rendered)
     uint32_t* sort_scratch;   // radix-sort tables for the P-sized sort
+    uint32_t* rect_packed;    // [P] tile rectangle x0 | y0 << 8 | width << 16 | height << 24 (visible Gaussians; grids up to 255 x 255 tiles)
+    uint32_t* rect_sorted;    // [P] the same words in depth order (written by the scan, read by the instance emission)
     uint32_t* n_visible;      // [1] Gaussians that survived the cull = valid prefix of order / point_offsets (device)
     static GeomState from(char*& p, size_t P) {
         GeomState g;
@@ -78,6 +86,8 @@ struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46
         g.point_offsets = carve<uint32_t>(p, P);
         g.scan_sums = carve<uint32_t>(p, (P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE + 8);
         g.sort_scratch = carve<uint32_t>(p, sort_scratch_words(P));
+        g.rect_packed = carve<uint32_t>(p, P);
+        g.rect_sorted = carve<uint32_t>(p, P);
         g.n_visible = g.sort_scratch + 4 * GSR_RADIX + 8;      // where radix_sort_u32's drop mode leaves the kept count
         return g;
     }

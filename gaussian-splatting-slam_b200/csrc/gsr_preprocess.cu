@@ -189,11 +189,15 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
                                                               uint8_t* __restrict__ clamped,
                                                               uint32_t* __restrict__ tiles_touched,
                                                               uint32_t* __restrict__ dkey,
-                                                              uint32_t* __restrict__ order) {
+                                                              uint32_t* __restrict__ order,
+                                                              uint32_t* __restrict__ rect_packed) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P) return;
     int my_radii = 0;
     uint32_t my_tiles = 0, my_key = 0xFFFFFFFFu;   // culled Gaussians sort to the end and emit nothing
+    uint32_t my_rect = 0;
+    float my_depth = 0.0f;
+    uint8_t my_clamp = 0;
     const dim3 grid((a.W + GSR_TILE - 1) / GSR_TILE, (a.H + GSR_TILE - 1) / GSR_TILE, 1);
     do {
         const float3 p_orig = {__ldg(a.means3D + 3 * idx), __ldg(a.means3D + 3 * idx + 1), __ldg(a.means3D + 3 * idx + 2)};
@@ -272,19 +276,27 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
             if (!(ex == ex) || !(ey == ey)) { ex = 1e30f; ey = 1e30f; }
         } else { ex = 1e30f; ey = 1e30f; }
 
-        depths[idx] = p_view.z;
+        my_depth = p_view.z;
         my_radii = my_radius;
         rec[3 * (size_t)idx + 0] = make_float4(point_image.x, point_image.y, ex, ey);
         rec[3 * (size_t)idx + 1] = make_float4(conic.x, conic.y, conic.z, opacity);
         rec[3 * (size_t)idx + 2] = make_float4(color.x, color.y, color.z, 1.0f / p_view.z);
-        clamped[idx] = cb;
+        my_clamp = cb;
         my_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
+        // the rectangle itself, for the scan and the instance emission (binning): they then need neither the record nor
+        // the radius of the Gaussian again. Only meaningful for grids up to 255 x 255 tiles (launch_binning checks).
+        my_rect = rect_min.x | (rect_min.y << 8) | ((rect_max.x - rect_min.x) << 16) | ((rect_max.y - rect_min.y) << 24);
         my_key = __float_as_uint(p_view.z);                        // rasterizer_impl.cu:102-104 depth bits
     } while (0);
+    // the small per-Gaussian arrays are written for EVERY Gaussian (zeros for culled ones): a warp then fills whole
+    // sectors, where visible-only stores leave partially written sectors that cost a DRAM read-modify-write each
     radii[idx] = my_radii;
-    tiles_touched[idx] = my_tiles;
+    if (tiles_touched != nullptr) tiles_touched[idx] = my_tiles;   // only kept when the rectangle cannot be packed
     dkey[idx] = my_key;
     order[idx] = (uint32_t)idx;
+    depths[idx] = my_depth;
+    clamped[idx] = my_clamp;
+    rect_packed[idx] = my_rect;
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means, const float* __restrict__ view,
@@ -734,12 +746,13 @@ int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t 
     PreArgs a;
     fill_pre_args(v, a);
     const int blocks = (v.P + 255) / 256;
+    uint32_t* tiles_touched = rect_packing_ok(v.W, v.H) ? nullptr : g.tiles_touched;
     if (sh16_fast(v))
         GSR_LAUNCH("preprocess_fwd", v.debug, s,
-                   (preprocess_fwd_kernel<true><<<blocks, 256, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, g.tiles_touched, g.dkey, g.order)));
+                   (preprocess_fwd_kernel<true><<<blocks, 256, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
     else
         GSR_LAUNCH("preprocess_fwd", v.debug, s,
-                   (preprocess_fwd_kernel<false><<<blocks, 256, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, g.tiles_touched, g.dkey, g.order)));
+                   (preprocess_fwd_kernel<false><<<blocks, 256, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
     return 0;
 }
 

@@ -369,7 +369,14 @@ def decode_state(P, R, W, H, geomBuffer, binningBuffer, imgBuffer, view_args=Non
     out["means2D"], out["extent"] = rec[:, 0:2], rec[:, 2:4]
     out["conic_opacity"], out["rgb"], out["invdepth_g"] = rec[:, 4:8], rec[:, 8:11], rec[:, 11]
     out["clamped"] = take(geomBuffer, go[2], P, torch.uint8, (P,))
-    out["tiles_touched"] = take(geomBuffer, go[3], 4 * P, torch.int32, (P,))
+    if (W + 15) // 16 <= 255 and (H + 15) // 16 <= 255 and len(go) > 7:
+        # grids up to 255 x 255 tiles: the library keeps the packed tile rectangle (x0 | y0 << 8 | w << 16 | h << 24)
+        # instead of the count; the reference's tiles_touched is its width x height
+        rect = take(geomBuffer, go[7], 4 * P, torch.int32, (P,))
+        out["tile_rect"] = rect
+        out["tiles_touched"] = ((rect >> 16) & 255) * ((rect >> 24) & 255)
+    else:
+        out["tiles_touched"] = take(geomBuffer, go[3], 4 * P, torch.int32, (P,))
     out["point_offsets"] = take(geomBuffer, go[4], 4 * P, torch.int32, (P,))
     out["order"] = take(geomBuffer, go[5], 4 * P, torch.int32, (P,))
     n = L.gsr_image_layout(C.c_int(W), C.c_int(H), off, 8)

@@ -227,6 +227,20 @@ def test_sh3_wide_image_ragged_edges():
     _case(sc, cam, (0.1, 0.4, 0.9))
 
 
+def test_strip_wider_than_255_tiles_takes_the_unpacked_rectangle_path():
+    """Binning packs a Gaussian's tile rectangle into 4 x 8 bits when the grid has at most 255 x 255 tiles; a 4128-pixel
+    wide strip (258 tiles) must take the other path (rectangle recomputed from record + radius at emission) and give
+    the same bit-identical binning against the reference CUDA build."""
+    sc = scenes.small_scene(P=4000, deg=1, spread=2.5, scale_lo=0.02, scale_hi=0.4)
+    cam = scenes.look_at_camera(4128, 48, math.radians(120), (0.1, 0.05, -2.0))
+    rng = np.random.default_rng(11)
+    dpix = rng.standard_normal((3, cam.H, cam.W)).astype(np.float32)
+    ours = _run_ours(sc, cam, (0.2, 0.1, 0.0), dpix=dpix)
+    assert ours["num_rendered"] > 1000
+    assert int(ours["state"]["tiles_touched"].astype(np.int64).sum()) == ours["num_rendered"]
+    _check_vs_reference_cuda(ours, sc, cam, (0.2, 0.1, 0.0), dpix, "strip")
+
+
 @pytest.mark.parametrize("deg", [1, 2])
 def test_partial_sh_degree(deg):
     sc = scenes.small_scene(P=1500, deg=3)
