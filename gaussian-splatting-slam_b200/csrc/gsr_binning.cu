@@ -176,30 +176,34 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(const uint32_t* __r
         }
     }
     if (__ballot_sync(0xffffffffu, n > 0) == 0u) return;
-    // lanes beyond P: end = end of the last valid lane so the search never selects them
+    // lanes beyond P: end = end of the last valid lane, so they never own a slot that is written
     const uint32_t last_end = __shfl_sync(0xffffffffu, end, min(31, P - 1 - (j - lane)));
     if (j >= P) end = last_end;
-    const uint32_t first = __shfl_sync(0xffffffffu, end - n, 0);
-    const float inv_bw = 1.0f / (float)bw;
-    for (uint32_t s = first + lane; __any_sync(0xffffffffu, s < last_end); s += 32) {
-        // owner = number of lanes whose range ends at or before s
-        int lo = 0;
-#pragma unroll
-        for (int step = 16; step > 0; step >>= 1) {
-            const uint32_t e = __shfl_sync(0xffffffffu, end, lo + step - 1);
-            if (e <= s) lo += step;
-        }
-        const int owner = min(lo, 31);
+    const uint32_t start = end - n;
+    const uint32_t first = __shfl_sync(0xffffffffu, start, 0);
+    const uint32_t xy = (uint32_t)x0 | ((uint32_t)y0 << 16);
+    // The lanes walk the warp's output range 32 slots at a time. Owner of slot s = number of Gaussians whose range ends
+    // at or before s. The ends are strictly increasing, so inside a window of 32 slots they are distinct bits: ONE warp-wide
+    // OR (REDUX) of those bits plus a running count of the ends before the window replaces a per-slot binary search over
+    // the lanes (five dependent shuffles); four shuffles then fetch the owner's id, range start, corner and width.
+    // The kernel was bound by the shuffle / LSU pipe (69 % busy) before this.
+    uint32_t before = 0;                            // ends below the window's first slot (warp-uniform)
+    for (uint32_t base = first; base < last_end; base += 32) {
+        const uint32_t rel = end - base;            // wraps to a huge value for ends below the window
+        const uint32_t mine = (rel < 32u && j < P) ? (1u << rel) : 0u;
+        const uint32_t ends = __reduce_or_sync(0xffffffffu, mine);
+        const uint32_t s = base + lane;
+        const int owner = min((int)(before + __popc(ends & (0xffffffffu >> (31 - lane)))), 31);
+        before += __popc(ends);
         const uint32_t og = __shfl_sync(0xffffffffu, g, owner);
-        const uint32_t oend = __shfl_sync(0xffffffffu, end, owner), on = __shfl_sync(0xffffffffu, n, owner);
-        const int ox0 = __shfl_sync(0xffffffffu, x0, owner), oy0 = __shfl_sync(0xffffffffu, y0, owner);
+        const uint32_t ostart = __shfl_sync(0xffffffffu, start, owner);
+        const uint32_t oxy = __shfl_sync(0xffffffffu, xy, owner);
         const int obw = __shfl_sync(0xffffffffu, bw, owner);
-        const float oinv = __shfl_sync(0xffffffffu, inv_bw, owner);
         if (s < last_end) {
-            const uint32_t k = s - (oend - on);                        // row-major index inside the rectangle
-            const int row = (int)(((float)k + 0.5f) * oinv);          // exact: k < 2^13, bw <= 2^7
-            const int col = (int)k - row * obw;
-            tile_keys[s] = (uint32_t)((oy0 + row) * gx + ox0 + col);
+            const uint32_t k = s - ostart;                             // row-major index inside the rectangle
+            const int row = (int)(((float)k + 0.5f) * __frcp_rn((float)obw));   // exact: the quotient stays >= 0.5 / 4096 away
+            const int col = (int)k - row * obw;                        //        from an integer, the product errs by < 1e-3 of that
+            tile_keys[s] = (uint32_t)(((int)(oxy >> 16) + row) * gx + (int)(oxy & 0xffffu) + col);
             vals[s] = og;
         }
     }
