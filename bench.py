@@ -57,6 +57,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
+    ap.add_argument("--no-fused-exchange", action="store_true",
+                    help="train workload on several GPUs: all-reduce + Adam on every rank instead of the one-launch exchange+Adam")
     ap.add_argument("--no-grad-sinks", action="store_true", help="let autograd accumulate (reference semantics) instead of in-kernel accumulation")
     return ap.parse_args()
 
@@ -200,13 +202,24 @@ class OursArm:
         self.color_host = torch.empty(3, args.height, args.width).pin_memory()
         self.last = None
         self.train = args.workload == "train"
+        self.fused_opt = False
         if self.train:
             from fused_ssim import fused_l1_ssim_loss
             import gsr_optim
             self.loss_fn = fused_l1_ssim_loss
             self.gt = torch.rand(3, args.height, args.width, generator=torch.Generator().manual_seed(7)).to(dev)
-            self.opt = gsr_optim.FusedAdam([{"params": [self.params[k]], "lr": lr, "name": k} for k, lr in TRAIN_LRS.items()],
-                                           lr=0.0, eps=1e-15)
+            self.fused_opt = self.bucket.peer is not None and not args.no_fused_exchange
+            if self.fused_opt:
+                # several GPUs: parameters move into peer memory as well and the exchange + Adam become ONE launch per
+                # rank (each rank updates 1 / world of the parameters and keeps 1 / world of the moments)
+                from view_parallel import ExchangeAdam, ParamBucket
+                pb = ParamBucket(self.params, self.bucket)
+                self.params = pb.tensors
+                self.bucket.params = pb.tensors
+                self.opt = ExchangeAdam(self.bucket, pb, TRAIN_LRS, eps=1e-15)
+            else:
+                self.opt = gsr_optim.FusedAdam([{"params": [self.params[k]], "lr": lr, "name": k} for k, lr in TRAIN_LRS.items()],
+                                               lr=0.0, eps=1e-15)
 
     def _settings(self, cam, view, proj, campos):
         return self.Settings(image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=self.bg,
@@ -231,9 +244,12 @@ class OursArm:
         self.means2D.grad = None
         for cam, (v, pj, cp) in zip(self.cams_host, self.cams_dev):
             self._view(self._settings(cam, v, pj, cp), self.dpix)
-        self.bucket.all_reduce()
-        if self.train:
-            self.opt.step()
+        if self.train and self.fused_opt:
+            self.opt.step()                       # gsr_exchange_adam_step: the exchange and the optimiser in one launch
+        else:
+            self.bucket.all_reduce()
+            if self.train:
+                self.opt.step()
 
     def step_e2e(self):
         """Same step, host buffers: every view's camera + dL/dpixel come from pinned host memory and its rendered image goes
@@ -292,9 +308,12 @@ class OursArm:
             e["used"][k].record(main)
             self.last = (color, radii)
         main.wait_stream(e["d2h"])
-        self.bucket.all_reduce()
-        if self.train:
-            self.opt.step()
+        if self.train and self.fused_opt:
+            self.opt.step()                       # gsr_exchange_adam_step: the exchange and the optimiser in one launch
+        else:
+            self.bucket.all_reduce()
+            if self.train:
+                self.opt.step()
 
     def state_of_view(self, i):
         """Forward of view i through the binding (outside any timed region) and its decoded scratch state."""
@@ -527,6 +546,7 @@ def _main(out_fd):
     else:
         arm = OursArm(args, sc, cams, dpix_host, dev)
     exchange_kind = getattr(getattr(arm, "bucket", None), "exchange", "collective")
+    fused_opt_used = bool(getattr(arm, "fused_opt", False))
 
     def barrier():
         if ref_world > 1:
@@ -641,7 +661,13 @@ def _main(out_fd):
 
     if rank == 0:
         kind = exchange_kind
-        exchange_desc = {"multimem": "gsr_allreduce_sum launch per rank (NVSwitch multicast reduction over symmetric memory)",
+        if fused_opt_used:
+            kind = kind + "+adam"
+        exchange_desc = {"multimem+adam": "gsr_exchange_adam_step launch per rank (gradient slice reduced through the NVSwitch multicast mapping, "
+                                          "Adam on the slice, parameters multicast back)",
+                         "peer+adam": "gsr_exchange_adam_step launch per rank (gradient slice from peer loads, Adam on the slice, "
+                                      "parameters to every replica by peer stores)",
+                         "multimem": "gsr_allreduce_sum launch per rank (NVSwitch multicast reduction over symmetric memory)",
                          "peer": "gsr_allreduce_sum launch per rank (NVLink peer loads/stores over symmetric memory)"}.get(
                              kind, "NCCL all-reduce")
         out = {"metric": METRIC, "value": round(value, 3), "unit": "views/s", "n_gpus": ref_world, "steps": args.steps,

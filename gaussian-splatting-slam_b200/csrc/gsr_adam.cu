@@ -22,17 +22,6 @@ constexpr int kAdamThreads = 256;
 constexpr int kAdamVec = 4;
 constexpr int kAdamPerCta = kAdamThreads * kAdamVec * 4;     // 4096 elements per CTA
 
-struct AdamHyper { float omb1, b2, omb2, eps; };      // 1 - beta1, beta2, 1 - beta2 (rounded from double, as torch does), eps
-
-__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamHyper h, float step_size,
-                                         float inv_sqrt_bc2) {
-    const float eps = h.eps;
-    m = m + (g - m) * h.omb1;
-    v = v * h.b2 + h.omb2 * g * g;
-    const float denom = sqrtf(v) * inv_sqrt_bc2 + eps;
-    p = p - step_size * (m / denom);
-}
-
 __global__ void __launch_bounds__(kAdamThreads) adam_kernel(const __grid_constant__ AdamTable t, const AdamHyper h,
                                                              const uint8_t* __restrict__ visible) {
     int gi = 0;

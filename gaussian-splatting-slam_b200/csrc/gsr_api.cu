@@ -332,6 +332,36 @@ int gsr_allreduce_sum(const gsr_peer_group* group, long long numel, int max_ctas
     return launch_allreduce_sum(g, numel, max_ctas, (cudaStream_t)stream);
 }
 
+static bool peer_group_ok(const gsr_peer_group& g, bool need_signal) {
+    if (g.world < 1 || g.world > GSR_COMM_MAX_PEERS || g.rank < 0 || g.rank >= g.world) return false;
+    for (int p = 0; p < g.world; p++) {
+        if (!g.buf[p] || (reinterpret_cast<uintptr_t>(g.buf[p]) & 15)) return false;
+        if (need_signal && (!g.signal[p] || (reinterpret_cast<uintptr_t>(g.signal[p]) & 3))) return false;
+    }
+    return (reinterpret_cast<uintptr_t>(g.multicast) & 15) == 0;
+}
+
+int gsr_exchange_adam_step(const gsr_peer_group* grads, const gsr_peer_group* params, float* exp_avg, float* exp_avg_sq,
+                           const gsr_adam_span* spans, int n_spans, double beta1, double beta2, double eps, long long numel,
+                           int max_ctas, void* stream) {
+    if (!grads || !params || numel < 0 || (numel & 3) || max_ctas < 0 || n_spans < 0 || n_spans > GSR_ADAM_MAX_SPANS) return GSR_E_BADARG;
+    if (!peer_group_ok(*grads, true) || !peer_group_ok(*params, false)) return GSR_E_BADARG;
+    if (grads->rank != params->rank || grads->world != params->world) return GSR_E_BADARG;
+    if ((grads->multicast == nullptr) != (params->multicast == nullptr)) return GSR_E_BADARG;   // one data path for both
+    if (numel / 4 > (1ll << 40)) return GSR_E_TOOLARGE;
+    if (numel == 0) return 0;
+    if (n_spans > 0 && !spans) return GSR_E_BADARG;
+    long long prev = 0;
+    for (int k = 0; k < n_spans; k++) {
+        if (spans[k].begin < prev || spans[k].end < spans[k].begin || spans[k].end > numel || (spans[k].begin & 3)) return GSR_E_BADARG;
+        prev = (spans[k].end + 3) & ~3ll;
+    }
+    if (!exp_avg || !exp_avg_sq || (reinterpret_cast<uintptr_t>(exp_avg) & 15) || (reinterpret_cast<uintptr_t>(exp_avg_sq) & 15))
+        return GSR_E_BADARG;
+    return launch_exchange_adam(*grads, *params, exp_avg, exp_avg_sq, spans, n_spans, beta1, beta2, eps, numel, max_ctas,
+                                (cudaStream_t)stream);
+}
+
 size_t gsr_densify_plan_bytes(int P) { return P < 0 ? 0 : densify_plan_bytes((size_t)P); }
 
 int gsr_densify_plan(int P, const float* opacity, const float* scaling, const float* grad_accum, const float* denom,

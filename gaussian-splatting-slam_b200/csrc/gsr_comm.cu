@@ -121,6 +121,88 @@ __global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_kernel(const __
     twin_barrier(a);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Exchange + Adam in one launch (gsr_exchange_adam_step): the reduce-scatter half of the exchange feeds the optimiser
+// directly and the all-gather half carries PARAMETERS instead of gradients. Rank r is the only one that touches slice r
+// of the moments, so they are stored (and streamed) once per box instead of once per rank.
+struct ExchangeAdamArgs {
+    CommArgs g;                                  // gradient buckets + signal pads + this rank's slice
+    float4* pbuf[GSR_COMM_MAX_PEERS];            // parameter buckets, same layout
+    float4* pmc;
+    float4* m;                                   // this rank's slice of exp_avg / exp_avg_sq: element i at [i - lo]
+    float4* v;
+    long long sb[GSR_ADAM_MAX_SPANS], se[GSR_ADAM_MAX_SPANS];      // parameter spans in 16-byte units
+    float step_size[GSR_ADAM_MAX_SPANS], inv_sqrt_bc2[GSR_ADAM_MAX_SPANS];
+    int n_spans;
+    AdamHyper h;
+};
+
+template <bool MULTICAST, int WORLD>
+__global__ void __launch_bounds__(kCommThreads, 2) exchange_adam_kernel(const __grid_constant__ ExchangeAdamArgs a) {
+    twin_barrier(a.g);
+    const long long stride = (long long)gridDim.x * kCommThreads;
+    const int world = WORLD > 0 ? WORLD : a.g.world;
+    constexpr int U = 2;
+    for (long long i0 = a.g.lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < a.g.hi; i0 += stride * U) {
+        float4 g[U], p[U], m[U], v[U];
+        int span[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const long long i = i0 + u * stride;
+            span[u] = -1;
+            if (i < a.g.hi) {
+#pragma unroll
+                for (int k = 0; k < GSR_ADAM_MAX_SPANS; k++)
+                    if (k < a.n_spans && i >= a.sb[k] && i < a.se[k]) span[u] = k;
+            }
+            if (span[u] >= 0) {
+                if (MULTICAST) g[u] = mc_ld_reduce(a.g.mc + i);
+                else g[u] = peer_ld(a.g.buf[0] + i);
+                p[u] = a.pbuf[a.g.rank][i];
+                m[u] = a.m[i - a.g.lo];
+                v[u] = a.v[i - a.g.lo];
+            }
+        }
+        if (!MULTICAST) {
+#pragma unroll
+            for (int q = 1; q < (WORLD > 0 ? WORLD : GSR_COMM_MAX_PEERS); q++) {
+                if (q < world) {
+                    float4 w[U];
+#pragma unroll
+                    for (int u = 0; u < U; u++)
+                        if (span[u] >= 0) w[u] = peer_ld(a.g.buf[q] + i0 + u * stride);
+#pragma unroll
+                    for (int u = 0; u < U; u++) {            // rank order, as gsr_allreduce_sum
+                        if (span[u] >= 0) {
+                            g[u].x = __fadd_rn(g[u].x, w[u].x); g[u].y = __fadd_rn(g[u].y, w[u].y);
+                            g[u].z = __fadd_rn(g[u].z, w[u].z); g[u].w = __fadd_rn(g[u].w, w[u].w);
+                        }
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (span[u] < 0) continue;
+            const long long i = i0 + u * stride;
+            const float ss = a.step_size[span[u]], ib = a.inv_sqrt_bc2[span[u]];
+            adam_one(p[u].x, g[u].x, m[u].x, v[u].x, a.h, ss, ib);
+            adam_one(p[u].y, g[u].y, m[u].y, v[u].y, a.h, ss, ib);
+            adam_one(p[u].z, g[u].z, m[u].z, v[u].z, a.h, ss, ib);
+            adam_one(p[u].w, g[u].w, m[u].w, v[u].w, a.h, ss, ib);
+            a.m[i - a.g.lo] = m[u];
+            a.v[i - a.g.lo] = v[u];
+            if (MULTICAST) mc_st(a.pmc + i, p[u]);
+            else {
+#pragma unroll
+                for (int q = 0; q < (WORLD > 0 ? WORLD : GSR_COMM_MAX_PEERS); q++)
+                    if (q < world) peer_st(a.pbuf[q] + i, p[u]);
+            }
+        }
+    }
+    twin_barrier(a.g);
+}
+
 void comm_slice(long long n16, int rank, int world, long long* lo, long long* hi) {
     const long long per = (n16 + world - 1) / world;
     const long long l = per * rank < n16 ? per * rank : n16;
@@ -165,6 +247,58 @@ int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas,
         GSR_LAUNCH("allreduce_sum_peer", false, s, (allreduce_sum_kernel<false, 8><<<grid, kCommThreads, 0, s>>>(a)));
     else
         GSR_LAUNCH("allreduce_sum_peer", false, s, (allreduce_sum_kernel<false, 0><<<grid, kCommThreads, 0, s>>>(a)));
+    return 0;
+}
+
+int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& params, float* exp_avg, float* exp_avg_sq,
+                         const gsr_adam_span* spans, int n_spans, double b1, double b2, double eps, long long numel, int max_ctas,
+                         cudaStream_t s) {
+    ExchangeAdamArgs a;
+    for (int p = 0; p < GSR_COMM_MAX_PEERS; p++) {
+        a.g.buf[p] = p < grads.world ? reinterpret_cast<float4*>(grads.buf[p]) : nullptr;
+        a.g.sig[p] = p < grads.world ? grads.signal[p] : nullptr;
+        a.pbuf[p] = p < params.world ? reinterpret_cast<float4*>(params.buf[p]) : nullptr;
+    }
+    a.g.mc = reinterpret_cast<float4*>(grads.multicast);
+    a.pmc = reinterpret_cast<float4*>(params.multicast);
+    a.g.rank = grads.rank;
+    a.g.world = grads.world;
+    const long long n16 = numel / 4;
+    comm_slice(n16, grads.rank, grads.world, &a.g.lo, &a.g.hi);
+    a.m = reinterpret_cast<float4*>(exp_avg);
+    a.v = reinterpret_cast<float4*>(exp_avg_sq);
+    a.n_spans = n_spans;
+    for (int k = 0; k < GSR_ADAM_MAX_SPANS; k++) {
+        a.sb[k] = k < n_spans ? spans[k].begin / 4 : 0;
+        a.se[k] = k < n_spans ? (spans[k].end + 3) / 4 : 0;
+        a.step_size[k] = k < n_spans ? spans[k].step_size : 0.f;
+        a.inv_sqrt_bc2[k] = k < n_spans ? spans[k].inv_sqrt_bc2 : 0.f;
+    }
+    a.h = AdamHyper{(float)(1.0 - b1), (float)b2, (float)(1.0 - b2), (float)eps};
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return (int)e;
+    }
+    const long long per = (n16 + grads.world - 1) / grads.world;
+    long long ctas = (per + (long long)kCommThreads * 2 - 1) / ((long long)kCommThreads * 2);
+    long long cap = max_ctas > 0 ? max_ctas : 2 * sms;
+    if (cap > GSR_COMM_MAX_CTAS) cap = GSR_COMM_MAX_CTAS;
+    if (ctas > cap) ctas = cap;
+    if (ctas < 1) ctas = 1;
+    const unsigned grid = (unsigned)ctas;
+    if (a.g.mc != nullptr)
+        GSR_LAUNCH("exchange_adam_multimem", false, s, (exchange_adam_kernel<true, 0><<<grid, kCommThreads, 0, s>>>(a)));
+    else if (grads.world == 2)
+        GSR_LAUNCH("exchange_adam_peer", false, s, (exchange_adam_kernel<false, 2><<<grid, kCommThreads, 0, s>>>(a)));
+    else if (grads.world == 4)
+        GSR_LAUNCH("exchange_adam_peer", false, s, (exchange_adam_kernel<false, 4><<<grid, kCommThreads, 0, s>>>(a)));
+    else if (grads.world == 8)
+        GSR_LAUNCH("exchange_adam_peer", false, s, (exchange_adam_kernel<false, 8><<<grid, kCommThreads, 0, s>>>(a)));
+    else
+        GSR_LAUNCH("exchange_adam_peer", false, s, (exchange_adam_kernel<false, 0><<<grid, kCommThreads, 0, s>>>(a)));
     return 0;
 }
 

@@ -34,6 +34,19 @@ void prof_end(cudaStream_t s);
         if (_ce != cudaSuccess) return (int)_ce;                                   \
     } while (0)
 
+// ---------------------------------------------------------------- Adam update (shared by gsr_adam.cu and gsr_comm.cu)
+struct AdamHyper { float omb1, b2, omb2, eps; };      // 1 - beta1, beta2, 1 - beta2 (rounded from double, as torch does), eps
+#ifdef __CUDACC__
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamHyper h, float step_size,
+                                         float inv_sqrt_bc2) {
+    const float eps = h.eps;
+    m = m + (g - m) * h.omb1;
+    v = v * h.b2 + h.omb2 * g * g;
+    const float denom = sqrtf(v) * inv_sqrt_bc2 + eps;
+    p = p - step_size * (m / denom);
+}
+#endif
+
 // ---------------------------------------------------------------- scratch layouts (private)
 template <typename T>
 static inline T* carve(char*& p, size_t count) {
@@ -179,6 +192,9 @@ int set_exact_cull(int on);
 int launch_cull_stats(const gsr_view& v, const GeomState& g, const BinningState& b, const ImageState& img,
                       unsigned long long* out, cudaStream_t s);
 int launch_adam(const gsr_adam_group* groups, int n, double b1, double b2, double eps, const uint8_t* visible, cudaStream_t s);
+int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& params, float* exp_avg, float* exp_avg_sq,
+                         const gsr_adam_span* spans, int n_spans, double b1, double b2, double eps, long long numel, int max_ctas,
+                         cudaStream_t s);
 int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas, cudaStream_t s);
 void comm_slice(long long n16, int rank, int world, long long* lo, long long* hi);
 int launch_exp_check(unsigned long long* mismatches_dev, cudaStream_t s);

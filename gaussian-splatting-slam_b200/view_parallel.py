@@ -34,10 +34,18 @@ class _PeerGroup(C.Structure):      # gsr_peer_group (include/gsr.h)
                 ("signal", C.c_void_p * GSR_COMM_MAX_PEERS), ("multicast", C.c_void_p)]
 
 
+class _AdamSpan(C.Structure):       # gsr_adam_span (include/gsr.h)
+    _fields_ = [("begin", C.c_longlong), ("end", C.c_longlong), ("step_size", C.c_float), ("inv_sqrt_bc2", C.c_float)]
+
+
 def _gsr():
     from diff_gaussian_rasterization import _C
     L = _C.lib()
     if not getattr(L, "_comm_bound", False):
+        L.gsr_exchange_adam_step.restype = C.c_int
+        L.gsr_exchange_adam_step.argtypes = [C.POINTER(_PeerGroup), C.POINTER(_PeerGroup), C.c_void_p, C.c_void_p,
+                                             C.POINTER(_AdamSpan), C.c_int, C.c_double, C.c_double, C.c_double,
+                                             C.c_longlong, C.c_int, C.c_void_p]
         L.gsr_comm_signal_bytes.restype = C.c_size_t
         L.gsr_comm_slice.restype = C.c_int
         L.gsr_comm_slice.argtypes = [C.c_longlong, C.c_int, C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
@@ -101,6 +109,102 @@ class PeerExchange:
 
     def all_reduce(self, max_ctas: int = 0):
         peer_all_reduce(self.desc, self.numel, max_ctas)
+
+
+def exchange_adam_raw(grads: "_PeerGroup", params: "_PeerGroup", exp_avg, exp_avg_sq, spans, beta1, beta2, eps, numel,
+                      max_ctas: int = 0, stream=None):
+    """One launch of gsr_exchange_adam_step. spans: list of (begin, end, step_size, inv_sqrt_bc2)."""
+    L, _C = _gsr()
+    arr = (_AdamSpan * max(1, len(spans)))()
+    for k, (b, e, ss, ib) in enumerate(spans):
+        arr[k] = _AdamSpan(int(b), int(e), float(ss), float(ib))
+    st = torch.cuda.current_stream().cuda_stream if stream is None else stream
+    _C._check(L.gsr_exchange_adam_step(C.byref(grads), C.byref(params), C.c_void_p(exp_avg.data_ptr()),
+                                       C.c_void_p(exp_avg_sq.data_ptr()), arr, len(spans), beta1, beta2, eps, numel,
+                                       max_ctas, C.c_void_p(st)), "gsr_exchange_adam_step")
+
+
+class ParamBucket:
+    """The Gaussian parameters as views of ONE flat buffer with the GradBucket's layout. When the gradient bucket lives
+    in peer memory so does this one, which is what lets `ExchangeAdam` write a rank's updated slice into every replica.
+    `tensors[name]` are leaf tensors (requires_grad) aliasing the flat storage; use them instead of the originals."""
+
+    def __init__(self, params: Dict[str, torch.Tensor], grads: "GradBucket", group=None):
+        if list(params.keys()) != list(grads.params.keys()):
+            raise ValueError("ParamBucket: parameter names / order differ from the gradient bucket")
+        self.peer = None
+        numel = grads.flat.numel()
+        if grads.peer is not None:
+            self.peer = PeerExchange(numel, grads.device, group, multicast=grads.peer.has_multicast)
+            if self.peer.has_multicast != grads.peer.has_multicast:
+                raise RuntimeError("ParamBucket: parameter and gradient buckets must use the same data path")
+            self.flat = self.peer.flat
+        else:
+            self.flat = torch.zeros(numel, dtype=torch.float32, device=grads.device)
+        self.offsets = dict(grads.offsets)
+        self.tensors = {}
+        with torch.no_grad():
+            for name, p in params.items():
+                o = self.offsets[name]
+                view = self.flat[o:o + p.numel()].view_as(p)
+                view.copy_(p)
+                self.tensors[name] = view.requires_grad_(True)
+        if self.peer is not None:
+            torch.cuda.synchronize(grads.device)
+            dist.barrier(group)                    # every replica initialised before anybody's kernel writes into it
+
+
+class ExchangeAdam:
+    """The exchange step and the optimiser step of view-parallel training as ONE launch per rank
+    (gsr_exchange_adam_step): rank r sums slice r of the gradient buckets, runs Adam on slice r of the parameters with
+    its own slice of the moments and writes the result into every replica. Same update as
+    `GradBucket.all_reduce()` followed by `gsr_optim.FusedAdam.step()` on every rank (torch.optim.Adam semantics:
+    bias correction by the step count, eps added after the square root; scene/gaussian_model.py:168 uses eps 1e-15),
+    bit for bit on the peer path. Moments are stored for the own slice only (1 / world of FusedAdam's state).
+    Without peer memory (one rank, gloo, GSR_EXCHANGE=nccl) it does exactly those two steps with full-size moments."""
+
+    def __init__(self, grads: "GradBucket", params: ParamBucket, lrs: Dict[str, float], betas=(0.9, 0.999), eps=1e-15,
+                 group=None):
+        self.grads, self.params, self.lrs = grads, params, dict(lrs)
+        self.betas, self.eps, self.group, self.t = betas, eps, group, 0
+        numel = grads.flat.numel()
+        self.fused = grads.peer is not None and params.peer is not None
+        if self.fused:
+            d = grads.peer.desc
+            lo, hi = comm_slice(numel, d.rank, d.world)
+        else:
+            lo, hi = 0, numel
+        self.lo, self.hi = lo, hi
+        n = max(hi - lo, 4)
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=grads.device)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=grads.device)
+
+    def _spans(self):
+        import math
+        b1, b2 = self.betas
+        out = []
+        for name, p in self.grads.params.items():
+            o = self.grads.offsets[name]
+            lr = self.lrs[name]
+            out.append((o, o + p.numel(), lr / (1.0 - b1 ** self.t), 1.0 / math.sqrt(1.0 - b2 ** self.t)))
+        return out
+
+    @torch.no_grad()
+    def step(self):
+        self.t += 1
+        spans = self._spans()
+        b1, b2 = self.betas
+        if self.fused:
+            exchange_adam_raw(self.grads.peer.desc, self.params.peer.desc, self.exp_avg, self.exp_avg_sq, spans, b1, b2,
+                              self.eps, self.grads.flat.numel())
+            return
+        import gsr_optim
+        self.grads.all_reduce(self.group)
+        entries = []
+        for (name, p), (b, e, ss, ib) in zip(self.grads.params.items(), spans):
+            row_len = p.numel() // p.shape[0] if p.dim() > 0 and p.shape[0] > 0 else 1
+            entries.append((self.params.flat[b:e], self.grads.flat[b:e], self.exp_avg[b:e], self.exp_avg_sq[b:e], row_len, ss, ib))
+        gsr_optim.adam_step_raw(entries, b1, b2, self.eps)
 
 
 def bind_rank_to_gpu_numa(device_index: int):

@@ -124,3 +124,30 @@ def test_grad_bucket_exchange_mode_is_validated():
     assert GradBucket(p).exchange == "collective"
     with pytest.raises(ValueError):
         GradBucket(p, exchange="carrier-pigeon")
+
+
+def test_exchange_adam_arguments_are_validated(gsr_lib):
+    """gsr_exchange_adam_step never launches on malformed input (include/gsr.h): mismatched groups, overlapping or
+    unordered spans, misaligned moments."""
+    import ctypes as C
+    from view_parallel import _AdamSpan, _PeerGroup, _gsr
+    L, _ = _gsr()
+
+    def grp(rank=0, world=2, mc=None):
+        g = _PeerGroup()
+        g.rank, g.world = rank, world
+        for p in range(world):
+            g.buf[p], g.signal[p] = 4096 * (p + 1), 65536 * (p + 1)
+        g.multicast = mc
+        return g
+    spans = (_AdamSpan * 2)(_AdamSpan(0, 100, 1e-3, 1.0), _AdamSpan(128, 256, 1e-3, 1.0))
+    call = lambda g, p, m, v, sp, n, numel: L.gsr_exchange_adam_step(C.byref(g), C.byref(p), C.c_void_p(m), C.c_void_p(v), sp, n,
+                                                                     0.9, 0.999, 1e-15, numel, 0, None)
+    assert call(grp(), grp(), 4096, 8192, spans, 2, 0) == 0                        # empty bucket: nothing to do
+    assert call(grp(), grp(rank=1), 4096, 8192, spans, 2, 256) == -1               # the two buckets disagree on the rank
+    assert call(grp(), grp(mc=1 << 20), 4096, 8192, spans, 2, 256) == -1           # one multicast, one not
+    assert call(grp(), grp(), 4100, 8192, spans, 2, 256) == -1                     # moments not 16-byte aligned
+    assert call(grp(), grp(), 4096, 8192, spans, 2, 200) == -1                     # span beyond the bucket
+    bad = (_AdamSpan * 2)(_AdamSpan(0, 130, 1e-3, 1.0), _AdamSpan(128, 256, 1e-3, 1.0))
+    assert call(grp(), grp(), 4096, 8192, bad, 2, 256) == -1                       # overlapping spans
+    assert call(grp(), grp(), 4096, 8192, spans, 9, 256) == -1                     # more spans than GSR_ADAM_MAX_SPANS

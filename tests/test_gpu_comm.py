@@ -4,6 +4,7 @@ barriers, the slice ownership and the rank-ordered summation are exercised exact
 variant needs a real NVSwitch group: tools/comm_check.py under torchrun covers it). Oracle: the sum in rank order,
 computed by torch on the same device, bit for bit."""
 import ctypes as C
+import math
 
 import pytest
 import torch
@@ -49,3 +50,57 @@ def test_emulated_ranks_on_one_device_sum_in_rank_order(world, numel, max_ctas):
 def test_slices_match_the_kernel_ownership():
     assert comm_slice(36, 0, 2) == (0, 20) and comm_slice(36, 1, 2) == (20, 36)
     assert comm_slice(4, 1, 2) == (4, 4)                        # fewer 16-byte units than ranks: empty slices are fine
+
+
+@pytest.mark.parametrize("world,sizes,max_ctas", [(2, (9003, 3001, 144048, 12004), 16), (3, (300, 100, 4800, 400), 4),
+                                                  (4, (30000, 10000, 480000, 40000), 24)])
+@pytest.mark.timeout(120)
+def test_exchange_adam_on_emulated_ranks_equals_allreduce_then_adam(world, sizes, max_ctas):
+    """gsr_exchange_adam_step (slice-wise gradient sum -> Adam on the slice -> parameters written into every replica)
+    against the two-step path it replaces: rank-ordered sum of the gradient buckets, then gsr_adam_step over the whole
+    bucket. Parameters on every rank and the moment slices must match bit for bit, over two consecutive steps; the
+    gradient buckets stay untouched; alignment padding between the parameter spans is left alone."""
+    import gsr_optim
+    from view_parallel import exchange_adam_raw
+    L, _ = _gsr()
+    dev = torch.device("cuda:0")
+    gen = torch.Generator(device=dev).manual_seed(world)
+    offs, off = [], 0
+    for n in sizes:
+        offs.append(off)
+        off += (n + 31) // 32 * 32
+    numel = off
+    lrs = [1.6e-4, 5e-2, 2.5e-3, 1e-3]
+    p0 = torch.randn(numel, device=dev, generator=gen)
+    pbufs = [p0.clone() for _ in range(world)]
+    pads = [torch.zeros(L.gsr_comm_signal_bytes() // 4, dtype=torch.int32, device=dev) for _ in range(world)]
+    slices = [comm_slice(numel, r, world) for r in range(world)]
+    ms = [torch.zeros(max(hi - lo, 4), device=dev) for lo, hi in slices]
+    vs = [torch.zeros(max(hi - lo, 4), device=dev) for lo, hi in slices]
+    ref_p, ref_m, ref_v = p0.clone(), torch.zeros(numel, device=dev), torch.zeros(numel, device=dev)
+    streams = [torch.cuda.Stream(dev) for _ in range(world)]
+    b1, b2, eps = 0.9, 0.999, 1e-15
+    for t in (1, 2):
+        gbufs = [torch.randn(numel, device=dev, generator=gen) * (0.1 + r) for r in range(world)]
+        for o, n in zip(offs, sizes):                       # padding carries no gradient
+            for g in gbufs:
+                g[o + n:(o + n + 31) // 32 * 32] = 0
+        keep = [g.clone() for g in gbufs]
+        gsum = gbufs[0].clone()
+        for r in range(1, world):
+            gsum = gsum + gbufs[r]
+        spans = [(o, o + n, lr / (1 - b1 ** t), 1 / math.sqrt(1 - b2 ** t)) for o, n, lr in zip(offs, sizes, lrs)]
+        gsr_optim.adam_step_raw([(ref_p[b:e], gsum[b:e], ref_m[b:e], ref_v[b:e], 1, ss, ib) for b, e, ss, ib in spans], b1, b2, eps)
+        torch.cuda.synchronize()
+        for r in range(world):
+            exchange_adam_raw(_group(gbufs, pads, r), _group(pbufs, pads, r), ms[r], vs[r], spans, b1, b2, eps, numel,
+                              max_ctas, stream=streams[r].cuda_stream)
+        torch.cuda.synchronize()
+        for r in range(world):
+            assert torch.equal(pbufs[r], ref_p), f"step {t} rank {r}: max diff {(pbufs[r] - ref_p).abs().max().item()}"
+            assert torch.equal(gbufs[r], keep[r]), "gradient bucket was modified"
+            lo, hi = slices[r]
+            assert torch.equal(ms[r][:hi - lo], ref_m[lo:hi]) and torch.equal(vs[r][:hi - lo], ref_v[lo:hi])
+        assert all(int(p.abs().sum()) == 0 for p in pads)
+    for o, n in zip(offs, sizes):                           # padding untouched
+        assert torch.equal(pbufs[0][o + n:(o + n + 31) // 32 * 32], p0[o + n:(o + n + 31) // 32 * 32])

@@ -96,6 +96,54 @@ def main():
     med, best = time_it(lambda: dist.all_reduce(flat))
     out["paths"]["nccl"] = {"available": True, "rel_l2": rel, "ms_median": med, "ms_best": best,
                             "link_GBps_per_rank_per_dir": numel * 4 * 2 * (world - 1) / world / med / 1e6}
+    # ---- exchange + Adam in one launch against all-reduce + gsr_adam_step on every rank
+    del flat, want, mine
+    torch.cuda.empty_cache()
+    try:
+        import gsr_optim
+        from view_parallel import ExchangeAdam, GradBucket, ParamBucket
+        P = args.gaussians
+        gen = torch.Generator(device=dev).manual_seed(7)              # replicated parameters: same seed on every rank
+        shapes = {"means3D": (P, 3), "shs": (P, 16, 3), "opacities": (P, 1), "scales": (P, 3), "rotations": (P, 4)}
+        lrs = {"means3D": 1.6e-4, "shs": 2.5e-3, "opacities": 5e-2, "scales": 5e-3, "rotations": 1e-3}
+        params = {k: torch.randn(*shp, device=dev, generator=gen).requires_grad_(True) for k, shp in shapes.items()}
+        bucket = GradBucket(params)
+        pb = ParamBucket(params, bucket)
+        bucket.params = pb.tensors
+        opt = ExchangeAdam(bucket, pb, lrs, eps=1e-15)
+        ref_p = {k: v.detach().clone().requires_grad_(True) for k, v in params.items()}
+        ref_bucket = GradBucket(ref_p, exchange="nccl")
+        ref_opt = gsr_optim.FusedAdam([{"params": [ref_p[k]], "lr": lr, "name": k} for k, lr in lrs.items()], lr=0.0, eps=1e-15)
+        ref_bucket.attach()
+        worst = 0.0
+        for step in range(2):
+            g = torch.Generator(device=dev).manual_seed(100 * step + rank)
+            grad = torch.randn(bucket.flat.numel(), device=dev, generator=g) * 1e-3
+            bucket.flat.copy_(grad)
+            ref_bucket.flat.copy_(grad)
+            torch.cuda.synchronize(); dist.barrier()
+            opt.step()
+            ref_bucket.all_reduce()
+            ref_opt.step()
+            torch.cuda.synchronize(); dist.barrier()
+            for k in shapes:
+                worst = max(worst, float((pb.tensors[k].detach() - ref_p[k].detach()).abs().max()))
+        same = pb.flat.clone()
+        dist.broadcast(same, 0)
+        ident = torch.tensor([int(torch.equal(same, pb.flat))], device=dev)
+        dist.all_reduce(ident, op=dist.ReduceOp.MIN)
+        fused_med, fused_best = time_it(opt.step)
+
+        def two_step():
+            ref_bucket.all_reduce()
+            ref_opt.step()
+        two_med, two_best = time_it(two_step)
+        out["exchange_adam"] = {"fused": opt.fused, "kind": bucket.exchange, "max_abs_param_diff_vs_allreduce_then_adam": worst,
+                                "parameters_identical_on_all_ranks": bool(ident.item()), "ms_fused_median": fused_med,
+                                "ms_allreduce_plus_adam_median": two_med, "moment_bytes_per_rank_fused": int(opt.exp_avg.numel() * 8),
+                                "moment_bytes_per_rank_two_step": int(bucket.flat.numel() * 8)}
+    except Exception as e:      # noqa: BLE001
+        out["exchange_adam"] = {"error": repr(e)[:400]}
     if rank == 0:
         line = json.dumps(out)
         print(line)
