@@ -80,18 +80,28 @@ __global__ void __launch_bounds__(kScanThreads) scan_chained_kernel(const uint32
     volatile uint32_t* vs = status;
     if (threadIdx.x == 0) vs[tile] = (tile == 0 ? kScanIncl : kScanOwn) | total;
     if (threadIdx.x < 32) {
+        // look-back, 128 predecessors per round trip: lane l reads tiles j - 4l .. j - 4l - 3 (nearest first). The front
+        // of finished (inclusive) prefixes advances one window per L2 round trip, so a window of 32 made the last of
+        // ~700 tiles wait for ~20 round trips.
         const int lane = threadIdx.x;
         uint32_t prefix = 0;
-        for (int j = tile - 1; j >= 0; j -= 32) {
-            const int idx = j - lane;
-            uint32_t st = kScanIncl;                       // before the first tile: inclusive prefix 0
-            if (idx >= 0) {
-                st = vs[idx];
-                while ((st >> 30) == 0u) { __nanosleep(20); st = vs[idx]; }
+        for (int j = tile - 1; j >= 0; j -= 128) {
+            uint32_t part = 0;                             // sum of this lane's words up to (and including) its first inclusive one
+            bool has_incl = false;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int idx = j - 4 * lane - q;
+                uint32_t st = kScanIncl;                   // before the first tile: inclusive prefix 0
+                if (idx >= 0) {
+                    st = vs[idx];
+                    while ((st >> 30) == 0u) { __nanosleep(20); st = vs[idx]; }
+                }
+                if (!has_incl) part += st & kScanVal;
+                has_incl = has_incl || (st >> 30) == 2u;
             }
-            const unsigned incl = __ballot_sync(0xffffffffu, (st >> 30) == 2u);
+            const unsigned incl = __ballot_sync(0xffffffffu, has_incl);
             const int first = incl ? __ffs(incl) - 1 : 31;
-            uint32_t val = lane <= first ? (st & kScanVal) : 0u;
+            uint32_t val = lane <= first ? part : 0u;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
             prefix += val;
@@ -116,9 +126,13 @@ __global__ void __launch_bounds__(kScanThreads) scan_chained_kernel(const uint32
 int launch_order_and_scan(const gsr_view& v, GeomState& g, uint32_t** total_dev, cudaStream_t s) {
     const int P = v.P;
     bool in_a = true;
-    GSR_MEMSET("memset_scan", s, g.scan_sums, 0, sizeof(uint32_t) * ((size_t)(P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE + 8));
+    // one memset clears the scan's status words and the depth sort's tables: they are carved next to each other
+    const size_t sort_words = 4 * GSR_RADIX + 64 + (size_t)radix_passes(32) * sort_tiles((size_t)P) * GSR_RADIX;
+    const char* zero_end = reinterpret_cast<const char*>(g.sort_scratch + sort_words);
+    GSR_MEMSET("memset_scan", s, g.scan_sums, 0, (size_t)(zero_end - reinterpret_cast<const char*>(g.scan_sums)));
     uint32_t* n_vis = nullptr;
-    int e = radix_sort_u32(g.dkey, g.order, g.dkey_tmp, g.order_tmp, P, 32, g.sort_scratch, &in_a, v.debug != 0, s, &n_vis);
+    int e = radix_sort_u32(g.dkey, g.order, g.dkey_tmp, g.order_tmp, P, 32, g.sort_scratch, &in_a, v.debug != 0, s, &n_vis,
+                           /*scratch_zeroed=*/true);
     if (e) return e;
     // 4 passes: the result is back in (dkey, order); its first *n_vis entries are the visible Gaussians
     if (n_vis != g.n_visible) return GSR_E_BADARG;              // layout contract between the two files

@@ -169,7 +169,8 @@ int launch_preprocess_backward(const gsr_view& v, const GeomState& g, const int*
 // Stable LSD radix sort of (u32 key, u32 value) pairs on key bits [0, total_bits). Ping-pongs between
 // (ka,va) and (kb,vb); *result_in_a tells where the sorted data ended up. scratch: sort_scratch_words(n).
 int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits,
-                   uint32_t* scratch, bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev = nullptr);
+                   uint32_t* scratch, bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev = nullptr,
+                   bool scratch_zeroed = false);
 static inline int radix_passes(int total_bits) { return (total_bits + 7) / 8; }
 int launch_sorted_keys_debug(const gsr_view& v, const GeomState& g, const BinningState& b, int R, uint64_t* keys_out,
                              cudaStream_t s);

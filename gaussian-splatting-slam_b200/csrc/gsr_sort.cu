@@ -309,7 +309,7 @@ static int launch_pass(const uint32_t* kin, const uint32_t* vin, uint32_t* kout,
 }
 
 int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits, uint32_t* scratch,
-                   bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev) {
+                   bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev, bool scratch_zeroed) {
     // n_valid_dev != NULL ("drop" sort, 32-bit keys only): pairs whose key is 0xFFFFFFFF are not part of the result;
     // the first pass compacts them away, the later passes run over the kept pairs only, and *n_valid_dev points at
     // their count (device). The tail of the output arrays beyond that count is unspecified.
@@ -323,7 +323,8 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
     uint32_t* ghist = scratch;                                  // [4][256]
     uint32_t* tickets = scratch + 4 * GSR_RADIX;                // [4] (+ padding)
     uint32_t* status = scratch + 4 * GSR_RADIX + 64;            // [passes][tiles][256]
-    GSR_MEMSET("memset_sort", s, scratch, 0, sizeof(uint32_t) * (4 * GSR_RADIX + 64 + (size_t)passes * tiles * GSR_RADIX));
+    if (!scratch_zeroed)
+        GSR_MEMSET("memset_sort", s, scratch, 0, sizeof(uint32_t) * (4 * GSR_RADIX + 64 + (size_t)passes * tiles * GSR_RADIX));
     const int hist_blocks = min((n / 4 + kSortThreads - 1) / kSortThreads, 148 * 8);
     GSR_LAUNCH("radix_hist", debug, s,
                (radix_hist_kernel<<<hist_blocks > 0 ? hist_blocks : 1, kSortThreads, 0, s>>>(ka, n, passes, total_bits, ghist, drop ? 1 : 0)));
