@@ -20,6 +20,8 @@ def short(name):
 
 # ---- launch list: share of the captured window per kernel
 rows = [r for r in csv.reader(open(launches)) if len(r) > 14 and r[0].isdigit()]
+# the work-counter kernels bench.py runs once after the timed region (roofline accounting) are not part of a step
+rows = [r for r in rows if "stats_kernel" not in r[4]]
 tot = defaultdict(lambda: [0, 0.0])
 for r in rows:
     k = short(r[4]); tot[k][0] += 1; tot[k][1] += float(r[14]) / 1e6
