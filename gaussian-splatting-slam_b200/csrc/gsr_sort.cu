@@ -325,7 +325,9 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
     uint32_t* status = scratch + 4 * GSR_RADIX + 64;            // [passes][tiles][256]
     if (!scratch_zeroed)
         GSR_MEMSET("memset_sort", s, scratch, 0, sizeof(uint32_t) * (4 * GSR_RADIX + 64 + (size_t)passes * tiles * GSR_RADIX));
-    const int hist_blocks = min((n / 4 + kSortThreads - 1) / kSortThreads, 148 * 8);
+    // a CTA pays a fixed price (clearing 32 KB of counters, flushing up to 1024 of them with global atomics), so it should
+    // see at least ~16K keys; 4 CTAs per SM at most
+    const int hist_blocks = min((n + 16383) / 16384, 148 * 4);
     GSR_LAUNCH("radix_hist", debug, s,
                (radix_hist_kernel<<<hist_blocks > 0 ? hist_blocks : 1, kSortThreads, 0, s>>>(ka, n, passes, total_bits, ghist, drop ? 1 : 0)));
     uint32_t *kin = ka, *vin = va, *kout = kb, *vout = vb;
