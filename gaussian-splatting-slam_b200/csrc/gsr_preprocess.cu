@@ -210,6 +210,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
             sc = V3{__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2)};
             q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
         }
+        const float opacity_in = __ldg(a.opacities + idx);       // used last, requested first
         const float3 p_view = xform43(p_orig, a.view);
         if (p_view.z <= 0.2f) {                                  // auxiliary.h:154
             if (a.prefiltered) {
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
             color = {__ldg(a.colors_precomp + 3 * idx), __ldg(a.colors_precomp + 3 * idx + 1),
                      __ldg(a.colors_precomp + 3 * idx + 2)};
         }
-        float opacity = __ldg(a.opacities + idx);
+        float opacity = opacity_in;
         if (a.antialiasing) opacity = opacity * sqrtf(fmaxf(0.000025f, det_cov / det));   // dr_aa (F1)
 
         // Conservative screen-space extent of the region where alpha >= 1/255 can hold, used by
@@ -354,8 +355,10 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
     float sc[3] = {0.f, 0.f, 0.f};
     float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
     int my_radius = 0;
+    uint8_t cbits_in = 0;
     if (inside) {
         my_radius = b.radii[idx];
+        cbits_in = b.clamped[idx];
         mean = make_float3(__ldg(a.means3D + 3 * idx), __ldg(a.means3D + 3 * idx + 1), __ldg(a.means3D + 3 * idx + 2));
         if (a.cov3D_precomp == nullptr) {
             sc[0] = __ldg(a.scales + 3 * idx); sc[1] = __ldg(a.scales + 3 * idx + 1); sc[2] = __ldg(a.scales + 3 * idx + 2);
@@ -553,7 +556,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
     }
     if (vis) {
         if (a.shs != nullptr || a.sh_dc != nullptr) {
-            const uint8_t cbits = b.clamped[idx];
+            const uint8_t cbits = cbits_in;
             dRGB[0] = (cbits & 1) ? 0.f : dcolor[0];
             dRGB[1] = (cbits & 2) ? 0.f : dcolor[1];
             dRGB[2] = (cbits & 4) ? 0.f : dcolor[2];
