@@ -151,3 +151,34 @@ def test_exchange_adam_arguments_are_validated(gsr_lib):
     bad = (_AdamSpan * 2)(_AdamSpan(0, 130, 1e-3, 1.0), _AdamSpan(128, 256, 1e-3, 1.0))
     assert call(grp(), grp(), 4096, 8192, bad, 2, 256) == -1                       # overlapping spans
     assert call(grp(), grp(), 4096, 8192, spans, 9, 256) == -1                     # more spans than GSR_ADAM_MAX_SPANS
+
+
+def test_param_bucket_aliases_flat_storage_with_the_gradient_layout():
+    """Host logic of the exchange+Adam path without peer memory: the parameter bucket copies the values, shares the
+    gradient bucket's offsets, and hands out LEAF tensors that alias its flat storage (what the rasterizer must be fed)."""
+    from view_parallel import ExchangeAdam, ParamBucket, bind_rank_to_gpu_numa
+    p = {"a": torch.randn(5, 3, requires_grad=True), "b": torch.randn(7, requires_grad=True)}
+    gb = GradBucket(p)
+    pb = ParamBucket(p, gb)
+    assert pb.peer is None and pb.offsets == gb.offsets and pb.flat.numel() == gb.flat.numel()
+    for k in p:
+        t = pb.tensors[k]
+        assert t.is_leaf and t.requires_grad and torch.equal(t.detach(), p[k].detach())
+        o = pb.offsets[k]
+        assert t.data_ptr() == pb.flat[o:].data_ptr()
+    with torch.no_grad():
+        pb.flat[pb.offsets["b"]] = 42.0
+    assert float(pb.tensors["b"].detach()[0]) == 42.0
+    gb.params = pb.tensors                      # gradients now attach to the aliased leaves
+    gb.attach()
+    (pb.tensors["a"].sum() * 2).backward()
+    assert torch.equal(gb.views["a"], torch.full((5, 3), 2.0))
+    with pytest.raises(ValueError):
+        ParamBucket({"b": p["b"], "a": p["a"]}, gb)          # order differs from the gradient bucket
+    opt = ExchangeAdam(gb, pb, {"a": 1e-3, "b": 1e-2})
+    assert not opt.fused and (opt.lo, opt.hi) == (0, gb.flat.numel())
+    opt.t = 3
+    spans = opt._spans()
+    assert [(b, e) for b, e, _, _ in spans] == [(gb.offsets["a"], gb.offsets["a"] + 15), (gb.offsets["b"], gb.offsets["b"] + 7)]
+    assert abs(spans[0][2] - 1e-3 / (1 - 0.9 ** 3)) < 1e-12 and abs(spans[1][3] - (1 - 0.999 ** 3) ** -0.5) < 1e-9
+    assert bind_rank_to_gpu_numa(0) is None     # no NVML device here: the affinity is left alone
