@@ -748,14 +748,15 @@ static bool sh16_fast(const gsr_view& v) {
 int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s) {
     PreArgs a;
     fill_pre_args(v, a);
-    const int blocks = (v.P + 255) / 256;
+    constexpr int kThreads = 128;
+    const int blocks = (v.P + kThreads - 1) / kThreads;
     uint32_t* tiles_touched = rect_packing_ok(v.W, v.H) ? nullptr : g.tiles_touched;
     if (sh16_fast(v))
         GSR_LAUNCH("preprocess_fwd", v.debug, s,
-                   (preprocess_fwd_kernel<true><<<blocks, 256, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
+                   (preprocess_fwd_kernel<true><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
     else
         GSR_LAUNCH("preprocess_fwd", v.debug, s,
-                   (preprocess_fwd_kernel<false><<<blocks, 256, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
+                   (preprocess_fwd_kernel<false><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
     return 0;
 }
 
