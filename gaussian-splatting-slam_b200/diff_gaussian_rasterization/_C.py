@@ -425,7 +425,7 @@ def set_exact_cull(on):
 def blend_stats(P, R, W, H, geomBuffer, binningBuffer, imgBuffer):
     """Work counters of a forward: (pairs up to each pixel's last contributor, contributing pairs)."""
     dev = geomBuffer.device
-    n = torch.zeros(6, dtype=torch.int64, device=dev)
+    n = torch.zeros(8, dtype=torch.int64, device=dev)
     if R > 0:
         view = _View()
         view.P, view.W, view.H = P, W, H
