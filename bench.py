@@ -403,9 +403,12 @@ def work_model(arm, args):
         # (P-sort: 4 passes) + (R-sort: rp passes): one histogram read of the keys per sort, then 8 B read + 8 B written
         # per pair and pass
         "radix_hist": ("hbm", 4.0 * (P + R)),
-        "onesweep_pass": ("hbm", 16.0 * (4 * P + rp * R)),
-        "scan_chained": ("hbm", 12.0 * P),
-        "emit_instances": ("hbm", 8.0 * P + 28.0 * visible + 8.0 * R),
+        # depth sort in drop mode: pass 1 reads all P pairs and writes the visible ones, passes 2-4 move visible pairs only
+        "onesweep_pass": ("hbm", 8.0 * P + 8.0 * visible + 3 * 16.0 * visible + 16.0 * rp * R),
+        # visible prefix only: order + packed rectangle read, offsets + depth-ordered rectangle written
+        "scan_chained": ("hbm", 16.0 * visible),
+        # order, offsets, rectangle streamed per visible Gaussian; (tile id, Gaussian id) written per instance
+        "emit_instances": ("hbm", 12.0 * visible + 8.0 * R),
         "tile_ranges": ("hbm", 4.0 * R + 8.0 * tiles),
         # 13 flop for every (pixel, list entry) pair the reference iterates (power + alpha test);
         # a contributing pair costs 22 flop in the forward and ~80 in the backward
