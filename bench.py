@@ -7,9 +7,17 @@ SH-degree-3 scene (config C3), reported as views/s over all GPUs a
 
 A STEP is one batch of `--views-per-step` (default 8) distinct cameras per GPU: forward + backward of every view
 through the public operator API (GaussianRasterizer + autograd), per-Gaussian gradients accumulated on the device,
-and -- for N > 1 -- one NCCL sum all-reduce of the 59-float/Gaussian gradient bucket (view-parallel data parallelism,
-weak scaling: per-GPU work is fixed). Inputs (708 MB of Gaussian parameters per replica) exceed the 126 MB L2, so no
-explicit flush is needed between iterations.
+and -- for N > 1 -- one sum exchange of the 59-float/Gaussian gradient bucket (view-parallel data parallelism: libgsr's own
+one-launch kernel over NVLink peer memory, gsr_allreduce_sum; NCCL only bootstraps the symmetric memory). `--scaling weak`
+(default) keeps the per-GPU work fixed; `--scaling strong` keeps the batch fixed at 64 views and splits it over the ranks.
+Inputs (708 MB of Gaussian parameters per replica) exceed the 126 MB L2, so no explicit flush is needed between iterations.
+
+Other workloads (`--workload`): train (config 3: + fused L1/SSIM loss per view + Adam per step), c1 (config 1: 10k Gaussians
+SH0, 256x256), c2 (config 2: 500k SH3, 1080p), slam (config 5: 640x480, map growing 200k -> 400k, distCUDA2 on every
+keyframe's new points), knn (distCUDA2 over 3M points). Each has the same `--impl reference` arm (the unmodified reference
+CUDA build, oracle/_ref). The default line also carries, outside the headline region, `drop_in_call_shape`,
+`train_step`, `ssim_ms` / `adam_ms` / `densify_ms` and -- for N > 1 -- `parity_multi_gpu` (rank 0 renders ALL views of the
+step alone and compares with the exchanged bucket).
 
 One JSON line is printed by rank 0. Keys beyond the base contract:
   roofline      dominant kernel of the step (by device time: CUDA events on the launching stream around every launch, in
@@ -51,9 +59,15 @@ def parse_args():
     ap.add_argument("--gaussians", type=int, default=3_000_000)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
-    ap.add_argument("--workload", default="raster", choices=["raster", "train"],
+    ap.add_argument("--workload", default="raster", choices=["raster", "train", "c1", "c2", "slam", "knn"],
                     help="raster: rasterizer forward+backward (BASELINE metric); train: + fused L1/SSIM loss per view and one "
-                         "Adam step per step (BASELINE config 3, 'full train-step')")
+                         "Adam step per step (BASELINE config 3, 'full train-step'); c1 / c2 / slam: BASELINE configs 1, 2, 5 "
+                         "with the reference's exact call shape; knn: distCUDA2 over --gaussians points")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --views-per-step views per GPU; strong: 8 x --views-per-step views in total, split over the ranks")
+    ap.add_argument("--no-extras", action="store_true", help="skip the secondary measurements of the default line")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the all-views-on-rank-0 gradient check")
+    ap.add_argument("--aa", action="store_true", help="c1 / c2 / slam, ours only: antialiasing + inverse-depth loss on")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
@@ -150,18 +164,29 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------------- workload
+def total_views(args, world):
+    """Views of one step over all ranks: weak scaling fixes the per-GPU batch, strong scaling the global one (64)."""
+    return args.views_per_step * (8 if args.scaling == "strong" else world)
+
+
 def build_workload(args, rank, world, dev):
     import torch
     import scenes
     sc = scenes.make_c3(P=args.gaussians)
-    n_views = args.views_per_step * world
+    n_views = total_views(args, world)
     cams = scenes.c3_cameras(n=n_views, W=args.width, H=args.height, jitter=0.05 if n_views > 8 else 0.0)
     from view_parallel import shard_views
     mine = [cams[i] for i in shard_views(n_views, rank, world)]
+    dpix_host = rank_dpix(args, rank, pinned=dev.type == "cuda")
+    return sc, mine, dpix_host, cams
+
+
+def rank_dpix(args, rank, pinned=False):
+    """dL/dpixel of every view a rank renders (seeded by the rank, so that another rank can restate it)."""
+    import torch
     g = torch.Generator().manual_seed(1000 + rank)
-    dpix_host = torch.randn(3, args.height, args.width, generator=g).pin_memory() if dev.type == "cuda" else \
-        torch.randn(3, args.height, args.width, generator=g)
-    return sc, mine, dpix_host
+    t = torch.randn(3, args.height, args.width, generator=g)
+    return t.pin_memory() if pinned else t
 
 
 def device_params(sc, dev):
@@ -176,6 +201,10 @@ def device_params(sc, dev):
 # stays the same from the first warm-up step to the last timed one. (With the real rates and a random target image
 # the scene drifts and consecutive steps time different workloads.)
 TRAIN_LRS = {"means3D": 0.0, "shs": 0.0, "opacities": 0.0, "scales": 0.0, "rotations": 0.0}
+# ... and ONE checked step with the reference's real rates (arguments/__init__.py:75-85: position_lr_init 1.6e-4,
+# feature_lr 2.5e-3, opacity_lr 5e-2 [upstream 0.025 / 0.05 depending on the version], scaling_lr 5e-3, rotation_lr 1e-3)
+# after the timed region: the parameters it produces are compared with torch.optim.Adam on the same gradients.
+CHECK_LRS = {"means3D": 1.6e-4, "shs": 2.5e-3, "opacities": 5e-2, "scales": 5e-3, "rotations": 1e-3}
 
 
 class OursArm:
@@ -402,14 +431,18 @@ def work_model(arm, args):
         "preprocess_fwd": ("hbm", 311.0 * visible + 20.0 * (P - visible)),
         # (P-sort: 4 passes) + (R-sort: rp passes): one histogram read of the keys per sort, then 8 B read + 8 B written
         # per pair and pass
-        "radix_hist": ("hbm", 4.0 * (P + R)),
+        # only the depth sort has a histogram kernel (one read of the P depth keys); the instance sort's digit histograms
+        # come from the tile table
+        "radix_hist": ("hbm", 4.0 * P),
         # depth sort in drop mode: pass 1 reads all P pairs and writes the visible ones, passes 2-4 move visible pairs only
-        "onesweep_pass": ("hbm", 8.0 * P + 8.0 * visible + 3 * 16.0 * visible + 16.0 * rp * R),
-        # visible prefix only: order + packed rectangle read, offsets + depth-ordered rectangle written
-        "scan_chained": ("hbm", 16.0 * visible),
-        # order, offsets, rectangle streamed per visible Gaussian; (tile id, Gaussian id) written per instance
-        "emit_instances": ("hbm", 12.0 * visible + 8.0 * R),
-        "tile_ranges": ("hbm", 4.0 * R + 8.0 * tiles),
+        "onesweep_depth": ("hbm", 8.0 * P + 8.0 * visible + 3 * 16.0 * visible),
+        # instance sort by tile id: 8 B read + 8 B written per pair and pass; the last pass writes no keys
+        "onesweep_tile": ("hbm", 16.0 * rp * R - 4.0 * R),
+        # scan + emission in one kernel: order + packed rectangle read, offsets written per visible Gaussian; (tile id,
+        # Gaussian id) written per instance; 4 RED operations per visible Gaussian into the difference array (L2)
+        "scan_emit": ("hbm", 12.0 * visible + 8.0 * R),
+        # one CTA: difference array -> ranges + digit histograms
+        "tile_table": ("hbm", 4.0 * (tiles + 200) + 8.0 * tiles),
         # 13 flop for every (pixel, list entry) pair the reference iterates (power + alpha test);
         # a contributing pair costs 22 flop in the forward and ~80 in the backward
         "blend_forward": ("fp32", 13.0 * (traversed - contributing) + 22.0 * contributing),
@@ -535,7 +568,20 @@ def _main(out_fd):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    sc, cams, dpix_host = build_workload(args, rank if ref_world > 1 else 0, ref_world, dev)
+    import bench_extra
+    if args.workload in ("c1", "c2", "slam", "knn"):
+        # single-view configs: no view-parallel axis; under torchrun rank 0 alone runs them
+        if ref_world > 1:
+            dist.barrier()
+        rc = 0
+        if rank == 0:
+            fn = bench_extra.run_knn if args.workload == "knn" else bench_extra.run_small
+            rc = fn(args, dev, emit, out_fd, ClockSampler, local)
+        if ref_world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return rc
+    sc, cams, dpix_host, all_cams = build_workload(args, rank if ref_world > 1 else 0, ref_world, dev)
     if args.impl == "reference":
         from oracle import ref_cuda
         if not ref_cuda.available():
@@ -612,9 +658,16 @@ def _main(out_fd):
     # headline region because ~60 event records per view cost the host ~5 % there; kernel durations are unaffected.
     ms_prof = timed(arm.step, args.steps, prof=True)[0] if prof else None
     clocks = sampler.stop() if rank == 0 else None
-    views = args.views_per_step * args.steps
+    views_rank = len(cams)                                   # views this rank renders per step
+    views_all = total_views(args, ref_world)                 # ... and all ranks together
+    views = views_rank * args.steps
     ms_per_step = ms_total / args.steps
-    value = ref_world * views / (ms_total / 1e3)
+    value = views_all * args.steps / (ms_total / 1e3)
+    parity = None
+    if ref_world > 1 and args.impl == "ours" and args.workload == "raster" and not args.no_parity:
+        arm.step()                                           # a fresh, un-profiled step: its exchanged bucket is what is checked
+        torch.cuda.synchronize()
+        parity = bench_extra.parity_multi_gpu(arm, args, all_cams, rank, ref_world, dev, rank_dpix)
 
     kernels, roof, roof_hbm, stats = None, None, None, None
     if prof:
@@ -627,7 +680,7 @@ def _main(out_fd):
                 peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
             except Exception:
                 pass
-            ms_view = ms_per_step / args.views_per_step
+            ms_view = ms_per_step / max(views_rank, 1)
             traffic = {}
             try:
                 traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
@@ -653,14 +706,24 @@ def _main(out_fd):
         arm.step_e2e()
         _dev_ms, wall_ms = timed(arm.step_e2e, args.steps)
         h2d, d2h = arm.e2e_bytes()
-        e2e = {"value": round(ref_world * views / (wall_ms / 1e3), 3), "unit": "views/s", "h2d_bytes_per_step": h2d,
+        e2e = {"value": round(views_all * args.steps / (wall_ms / 1e3), 3), "unit": "views/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "timing": "host wall clock around K steps incl. pinned H2D/D2H, max over ranks"}
 
-    cb = None
-    if rank == 0 and world == 1 and args.impl == "ours" and not args.no_cpu_baseline:
+    spec_stats = arm._C.speculation_stats() if args.impl == "ours" else None
+    fp32_peak = None
+    if rank == 0 and args.impl == "ours":
+        try:
+            fp32_peak = arm._C.fp32_peak_tflops(dev)
+        except Exception:       # noqa: BLE001
+            fp32_peak = None
+    extras, cb = None, None
+    if rank == 0 and world == 1 and args.impl == "ours":
         del arm
         torch.cuda.empty_cache()
-        cb = cpu_baseline(args)
+        if args.workload == "raster" and not args.no_extras:
+            extras = bench_extra.secondary(args, sc, cams, dpix_host, dev, OursArm, kernel_table, CHECK_LRS)
+        if not args.no_cpu_baseline:
+            cb = cpu_baseline(args)
 
     if rank == 0:
         kind = exchange_kind
@@ -674,14 +737,15 @@ def _main(out_fd):
                          "peer": "gsr_allreduce_sum launch per rank (NVLink peer loads/stores over symmetric memory)"}.get(
                              kind, "NCCL all-reduce")
         out = {"metric": METRIC, "value": round(value, 3), "unit": "views/s", "n_gpus": ref_world, "steps": args.steps,
-               "warmup": args.warmup, "warmup_steps_run": warm_run, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "weak",
+               "warmup": args.warmup, "warmup_steps_run": warm_run, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True,
+               "scaling": args.scaling,
                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-               "fwd_bwd_ms_per_iter": round(ms_per_step / args.views_per_step, 4),
+               "fwd_bwd_ms_per_iter": round(ms_per_step / max(views_rank, 1), 4),
                "config": {"workload": f"C3: {args.gaussians} Gaussians SH3 (Mip-NeRF360-scale mixture, seed 2), "
                                       f"{args.width}x{args.height}, orbit cameras; rasterizer forward+backward" +
                                       ("" if args.workload == "raster" else
                                        " + fused L1/SSIM loss per view + one Adam step over all parameters per step (full train-step)"),
-                          "views_per_step_per_gpu": args.views_per_step, "global_views_per_step": args.views_per_step * ref_world,
+                          "views_per_step_per_gpu": views_rank, "global_views_per_step": views_all,
                           "parallelism": f"view-parallel dp{ref_world}, replicated Gaussians" +
                                          (f", one {exchange_desc} of 59 floats/Gaussian per step" if ref_world > 1 else ""),
                           "l2": "inputs (708 MB parameters + 300 MB scratch per view) exceed the 126 MB L2; no explicit flush"},
@@ -704,6 +768,26 @@ def _main(out_fd):
             out["cpu_baseline"] = cb
             out["workload_stats"] = stats
             out["kernels"] = kernels
+            if parity is not None:
+                out["parity_multi_gpu"] = parity
+            if extras:
+                out.update(extras)
+            if fp32_peak:
+                out["fp32_simt_peak_measured_tflops"] = round(fp32_peak, 2)
+                for r_ in (roof,):
+                    if r_ and r_.get("bound") == "fp32":
+                        r_["peak"] = round(fp32_peak, 2)
+                        r_["frac"] = round(r_["achieved"] / fp32_peak, 4)
+                        r_["peak_source"] = ("measured in this run: gsr_debug_fp32_peak, 16 independent FFMA chains per thread, "
+                                             "8 x 256 threads per SM, CUDA events (MEASURED_PEAKS.json has no SIMT figure)")
+                if kernels:
+                    for k in ("blend_forward", "blend_backward"):
+                        if k in kernels and kernels[k].get("frac_of_roofline") is not None:
+                            kernels[k]["frac_of_roofline"] = round(kernels[k]["frac_of_roofline"] * FP32_PEAK_TFLOPS / fp32_peak, 4)
+            try:
+                out["speculation"] = dict(zip(("estimate_held", "repeated", "counted_first"), spec_stats))
+            except Exception:       # noqa: BLE001
+                pass
         emit(out_fd, out)
     if ref_world > 1:
         dist.destroy_process_group()

@@ -1,0 +1,350 @@
+"""bench_extra.py -- the parts of bench.py beyond the headline C3 line:
+
+  * the small / other BASELINE configs with their own reference arm (`--workload c1 | c2 | slam | knn`),
+  * `parity_multi_gpu` (N > 1: rank 0 renders ALL views of the step alone and compares with the exchanged bucket),
+  * the secondary measurements of the default line (`drop_in_call_shape`, `train_step` with one CHECKED optimiser
+    step, `ssim_ms`, `adam_ms`, `densify_ms`).
+
+Reference lines: config 1 = one 256x256 camera over 10k SH0 Gaussians, config 2 = 500k SH3 at 1080p
+(BASELINE.json:configs), config 5 = the SLAM loop of train_sdu6.py:39-83 (640x480 ORB-SLAM poses, a map that grows by a
+batch of points per keyframe whose initial scales come from distCUDA2, scene/gaussian_model.py:140). All of them use
+the REFERENCE'S call shape in both arms: fresh gradient tensors per view (optimizer.zero_grad(set_to_none=True),
+train.py:176), no grad_sinks, colour loss only and antialiasing off (the vendored rasterizer has neither; `--aa`
+reports ours with both on beside it).
+"""
+import json
+import math
+import os
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+SMALL_METRICS = {
+    "c1": "rasterizer fwd+bwd views/s, config 1: 10k Gaussians SH0, 256x256, one camera",
+    "c2": "rasterizer fwd+bwd views/s, config 2: 500k Gaussians SH3, 1920x1080",
+    "slam": "SLAM mapping keyframes/s, config 5: 640x480, map growing 200k -> 400k Gaussians (25k per keyframe), "
+            "distCUDA2 on the new points + rasterizer fwd+bwd per keyframe",
+    "knn": "distCUDA2 Mpoints/s (simple-knn initial-scale kernel)",
+}
+
+
+# ----------------------------------------------------------------------------------------------- small workloads
+class SmallArm:
+    """One step = every view of the workload once: forward + backward through the public operator API of `impl`."""
+
+    def __init__(self, args, impl, dev):
+        import torch
+        import scenes
+        self.torch, self.dev, self.impl, self.args = torch, dev, impl, args
+        wl = args.workload
+        V = args.views_per_step
+        if wl == "c1":
+            sc = scenes.make_c1()
+            cams = [scenes.c1_camera()] * V
+            sizes = [sc.means3D.shape[0]] * V
+            self.new_points = None
+        elif wl == "c2":
+            sc = scenes.make_c2()
+            cams = [scenes.orbit_camera(1920, 1080, 70.0, 4.0, 35.0 + 360.0 * i / V) for i in range(V)]
+            sizes = [sc.means3D.shape[0]] * V
+            self.new_points = None
+        else:                                   # slam
+            per = 25_000
+            sc = scenes.make_c5(P=200_000 + per * V)
+            cams = [scenes.c5_camera(k) for k in range(V)]
+            sizes = [200_000 + per * (k + 1) for k in range(V)]
+            self.new_points = [(s - per, s) for s in sizes]
+        self.deg, self.cams, self.sizes = sc.sh_degree, cams, sizes
+        names = ("means3D", "shs", "opacities", "scales", "rotations")
+        full = {n: getattr(sc, n).to(dev).contiguous() for n in names}
+        self.full = full
+        # leaf tensors per map size (slices share storage with the full map: no copies in the timed region)
+        self.leaves = {}
+        for sz in sorted(set(sizes)):
+            self.leaves[sz] = {n: full[n][:sz].detach().requires_grad_(True) for n in names}
+            self.leaves[sz]["means2D"] = torch.zeros(sz, 3, device=dev, requires_grad=True)
+        self.bg = torch.zeros(3, device=dev)
+        self.cams_dev = [(c.viewmatrix.to(dev), c.projmatrix.to(dev), c.campos.to(dev)) for c in cams]
+        g = torch.Generator().manual_seed(5)
+        self.dpix = torch.randn(3, cams[0].H, cams[0].W, generator=g).to(dev)
+        self.dinv = torch.randn(1, cams[0].H, cams[0].W, generator=g).to(dev)
+        self.aa = bool(args.aa) and impl == "ours"
+        if impl == "ours":
+            from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, _C
+            from simple_knn._C import distCUDA2
+            self._C, self.Settings, self.Rasterizer, self.dist2 = _C, GaussianRasterizationSettings, GaussianRasterizer, distCUDA2
+        else:
+            from oracle import ref_cuda
+            self.fn = ref_cuda.autograd_function()
+            self.dist2 = ref_cuda.dist2
+            self._C = None
+        self.last = None
+
+    def step(self):
+        torch = self.torch
+        for i, (cam, (v, pj, cp)) in enumerate(zip(self.cams, self.cams_dev)):
+            p = self.leaves[self.sizes[i]]
+            for t in p.values():
+                t.grad = None                                   # train.py:176 optimizer.zero_grad(set_to_none=True)
+            if self.new_points is not None:                     # gaussian_model.py:140 on the keyframe's new points
+                lo, hi = self.new_points[i]
+                self.last_d2 = self.dist2(self.full["means3D"][lo:hi])
+            if self.impl == "ours":
+                st = self.Settings(image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=self.bg,
+                                   scale_modifier=1.0, viewmatrix=v, projmatrix=pj, sh_degree=self.deg, campos=cp,
+                                   prefiltered=False, debug=False, antialiasing=self.aa)
+                color, radii, invd = self.Rasterizer(st)(means3D=p["means3D"], means2D=p["means2D"], opacities=p["opacities"],
+                                                         shs=p["shs"], scales=p["scales"], rotations=p["rotations"])
+                if self.aa:
+                    torch.autograd.backward([color, invd], [self.dpix, self.dinv])
+                else:
+                    torch.autograd.backward([color], [self.dpix])
+            else:
+                color, radii = self.fn.apply(p["means3D"], p["means2D"], p["shs"], p["opacities"], p["scales"], p["rotations"],
+                                             dict(bg=self.bg, viewmatrix=v, projmatrix=pj, campos=cp, tanfovx=cam.tanfovx,
+                                                  tanfovy=cam.tanfovy, H=cam.H, W=cam.W, sh_degree=self.deg))
+                torch.autograd.backward([color], [self.dpix])
+            self.last = (color, radii)
+
+    def launches(self):
+        return self._C.launch_count() if self._C is not None else 0
+
+
+def _timed_steps(torch, fn, steps):
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3
+
+
+def run_small(args, dev, emit, out_fd, ClockSampler, local):
+    """`--workload c1 | c2 | slam`: one JSON line, same keys as the headline line (single GPU; N > 1 runs replicas only
+    on rank 0 -- these configs are single-view by definition)."""
+    import torch
+    arm = SmallArm(args, args.impl, dev)
+    for _ in range(max(args.warmup, 3)):
+        arm.step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = arm.launches()
+    ms, wall = _timed_steps(torch, arm.step, args.steps)
+    launches = arm.launches() - l0
+    kernels = None
+    if args.impl == "ours" and not args.no_kernel_timing:
+        arm._C.profile_enable(True)
+        _timed_steps(torch, arm.step, args.steps)
+        arm._C.profile_enable(False)
+        kernels = {}
+        for line in arm._C.profile_report().strip().splitlines():
+            name, n, t = line.split()
+            kernels[name] = {"launches_per_view": round(int(n) / (args.steps * args.views_per_step), 3),
+                             "ms_per_view": round(float(t) / (args.steps * args.views_per_step), 5)}
+    clocks = sampler.stop()
+    views = args.steps * args.views_per_step
+    value = views / (ms / 1e3)
+    unit = "keyframes/s" if args.workload == "slam" else "views/s"
+    out = {"metric": SMALL_METRICS[args.workload], "value": round(value, 2), "unit": unit, "n_gpus": 1, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4), "ms_per_view": round(ms / views, 5),
+           "host_wall_ms_per_view": round(wall / views, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32", "data": "synthetic",
+           "config": {"workload": SMALL_METRICS[args.workload], "views_per_step": args.views_per_step,
+                      "call_shape": "the reference's: fresh gradient tensors per view, colour loss, no grad_sinks" +
+                                    ("; antialiasing + inverse-depth loss ON (ours only)" if arm.aa else "; antialiasing off"),
+                      "l2": "config-defined sizes: c1 (1 MB) and slam (50 MB) fit the 126 MB L2 by definition of the config; "
+                            "every view still runs its full kernel chain"},
+           "clocks": clocks, "gpu_launches": launches if args.impl == "ours" else None,
+           "e2e": {"value": round(views / (wall / 1e3), 2), "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                   "note": "host wall clock of the same loop (these configs are host-launch bound); cameras resident"}}
+    if args.impl == "reference":
+        out["impl"] = "reference"
+        out["cpu_baseline"] = {"value": out["value"], "unit": unit, "cores": 0, "kind": "reference",
+                               "sample": "unmodified reference CUDA rasterizer / simple-knn (oracle/_ref) on one B200, same step"}
+    else:
+        out["kernels"] = kernels
+        if args.workload != "c2":
+            out["speculation"] = dict(zip(("estimate_held", "repeated", "counted_first"), arm._C.speculation_stats()))
+    emit(out_fd, out)
+    return 0
+
+
+def run_knn(args, dev, emit, out_fd, ClockSampler, local):
+    """`--workload knn`: distCUDA2 over the positions of the C3 scene (simple_knn.cu:186-222)."""
+    import torch
+    import scenes
+    pts = scenes.make_c3(P=args.gaussians).means3D.to(dev).contiguous()
+    if args.impl == "ours":
+        from simple_knn._C import distCUDA2 as fn
+    else:
+        from oracle import ref_cuda
+        fn = ref_cuda.dist2
+    for _ in range(max(args.warmup, 3)):
+        out_t = fn(pts)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms, wall = _timed_steps(torch, lambda: fn(pts), args.steps)
+    clocks = sampler.stop()
+    value = args.gaussians * args.steps / (ms / 1e3) / 1e6
+    out = {"metric": SMALL_METRICS["knn"], "value": round(value, 2), "unit": "Mpoints/s", "n_gpus": 1, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"distCUDA2 over the {args.gaussians} positions of the C3 scene (36 MB, fits L2; one call per step)"},
+           "clocks": clocks, "gpu_launches": None,
+           "e2e": {"value": round(args.gaussians * args.steps / (wall / 1e3) / 1e6, 2), "unit": "Mpoints/s",
+                   "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "checksum": float(out_t.double().sum())}
+    if args.impl == "reference":
+        out["impl"] = "reference"
+        out["cpu_baseline"] = {"value": out["value"], "unit": "Mpoints/s", "cores": 0, "kind": "reference",
+                               "sample": "unmodified reference simple-knn CUDA build (oracle/_ref/ref_knn_C.so) on one B200"}
+    emit(out_fd, out)
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------- multi-GPU parity
+def parity_multi_gpu(arm, args, all_cams, rank, world, dev, rank_dpix):
+    """the summed gradients of n GPUs against ONE GPU over the same views, rel-L2 <= 1e-4 per tensor.
+    Called right after a step: arm.bucket holds the exchanged sums. Rank 0 renders every view of the step alone (each
+    with the dL/dpixel of the rank that owned it) into a private bucket; all ranks compare checksums of their copies."""
+    import torch
+    import torch.distributed as dist
+    from view_parallel import GradBucket, shard_views
+    flat = arm.bucket.flat
+    # identical bits on every rank: compare two independent 64-bit checksums of the raw words
+    words = flat.view(torch.int32).to(torch.int64)
+    sig = torch.stack([words.sum(), (words * (torch.arange(words.numel(), device=dev) % 8191 + 1)).sum()])
+    sigs = [torch.zeros_like(sig) for _ in range(world)]
+    dist.all_gather(sigs, sig)
+    identical = all(bool(torch.equal(s, sigs[0])) for s in sigs)
+    res = {"identical_on_all_ranks": identical}
+    if rank == 0:
+        exchanged = {k: v.detach().clone() for k, v in arm.bucket.views.items()}
+        params = {k: t.detach().clone().requires_grad_(True) for k, t in arm.params.items()}
+        solo = GradBucket(params, exchange="nccl")                  # plain device memory, no collective in the constructor
+        m2 = torch.zeros_like(params["means3D"], requires_grad=True)
+        n_views = len(all_cams)
+        for r in range(world):                                      # rank by rank: one dL/dpixel image resident at a time
+            dpix = rank_dpix(args, r).to(dev)
+            for i in shard_views(n_views, r, world):
+                cam = all_cams[i]
+                st = arm._settings(cam, cam.viewmatrix.to(dev), cam.projmatrix.to(dev), cam.campos.to(dev))
+                color, _radii, _ = arm.Rasterizer(st)(means3D=params["means3D"], means2D=m2, opacities=params["opacities"],
+                                                      shs=params["shs"], scales=params["scales"], rotations=params["rotations"],
+                                                      grad_sinks=solo.views)
+                torch.autograd.backward([color], [dpix])
+        torch.cuda.synchronize()
+        rel = {}
+        for k, v in solo.views.items():
+            d = (exchanged[k].double() - v.double()).norm()
+            rel[k] = float(d / v.double().norm().clamp_min(1e-30))
+        res.update({"rel_l2_per_tensor": {k: float(f"{x:.3e}") for k, x in rel.items()}, "max": float(f"{max(rel.values()):.3e}"),
+                    "views_checked": n_views, "bar": 1e-4,
+                    "how": "rank 0 renders all views of the step alone (in-kernel accumulation, same kernels) and compares "
+                           "with the bucket the exchange left on it; checksums of the raw bucket words compared over all ranks"})
+        del solo, params, exchanged
+        torch.cuda.empty_cache()
+    dist.barrier()
+    return res
+
+
+# ----------------------------------------------------------------------------------------------- secondary measurements
+def checked_adam_step(arm, lrs):
+    """One optimiser step with the reference's real learning rates on the gradients of the last step, against
+    torch.optim.Adam (the reference's optimiser, scene/gaussian_model.py:168) on copies of the same tensors."""
+    import torch
+    import gsr_optim
+    names = list(arm.params.keys())
+    p_ours = {k: arm.params[k].detach().clone().requires_grad_(True) for k in names}
+    p_ref = {k: arm.params[k].detach().clone().requires_grad_(True) for k in names}
+    grads = {k: arm.bucket.views[k].detach().clone() for k in names}
+    ours = gsr_optim.FusedAdam([{"params": [p_ours[k]], "lr": lrs[k], "name": k} for k in names], lr=0.0, eps=1e-15)
+    ref = torch.optim.Adam([{"params": [p_ref[k]], "lr": lrs[k], "name": k} for k in names], lr=0.0, eps=1e-15)
+    worst, moved = {}, {}
+    for step in range(2):                                           # two steps: the second one has non-zero moments
+        for k in names:
+            p_ours[k].grad = grads[k] * (1.0 + 0.5 * step)
+            p_ref[k].grad = grads[k] * (1.0 + 0.5 * step)
+        ours.step()
+        ref.step()
+    torch.cuda.synchronize()
+    for k in names:
+        worst[k] = float((p_ours[k].detach() - p_ref[k].detach()).abs().max() / lrs[k])
+        moved[k] = float((p_ref[k].detach() - arm.params[k].detach()).abs().max() / lrs[k])
+    ok = all(w <= 1e-3 for w in worst.values()) and all(m > 0.5 for m in moved.values())
+    return {"lrs": lrs, "steps": 2, "max_abs_diff_over_lr_vs_torch_adam": {k: float(f"{v:.3e}") for k, v in worst.items()},
+            "max_update_over_lr": {k: round(v, 3) for k, v in moved.items()}, "ok": ok,
+            "bar": "parameters after two steps within 1e-3 learning rates of torch.optim.Adam, every tensor moved"}
+
+
+def secondary(args, sc, cams, dpix_host, dev, OursArm, kernel_table, lrs):
+    """drop_in_call_shape, train_step (+ checked optimiser step), ssim_ms / adam_ms, densify_ms. A few steps each, outside
+    the headline region; every arm is freed before the next one is built."""
+    import copy
+    import sys
+    import torch
+    out = {}
+    steps = 3
+
+    def run(a2):
+        arm = OursArm(a2, sc, cams, dpix_host, dev)
+        for _ in range(3):
+            arm.step()
+        ms, _ = _timed_steps(torch, arm.step, steps)
+        return arm, ms / steps
+
+    try:
+        a2 = copy.copy(args)
+        a2.no_grad_sinks = True
+        arm, ms = run(a2)
+        out["drop_in_call_shape"] = {"value": round(args.views_per_step / (ms / 1e3), 2), "unit": "views/s",
+                                     "ms_per_view": round(ms / args.views_per_step, 4),
+                                     "what": "same step with the reference's exact call shape: fresh gradient tensors per view, "
+                                             "autograd accumulates (no grad_sinks keyword)"}
+        del arm
+        torch.cuda.empty_cache()
+    except Exception as e:      # noqa: BLE001 - secondary numbers must not take the headline line down
+        out["drop_in_call_shape"] = {"error": repr(e)[:300]}
+    try:
+        a2 = copy.copy(args)
+        a2.workload = "train"
+        arm, ms = run(a2)
+        arm._C.profile_enable(True)
+        _timed_steps(torch, arm.step, steps)
+        arm._C.profile_enable(False)
+        kt = kernel_table(arm._C.profile_report(), steps * args.views_per_step)
+        out["train_step"] = {"value": round(args.views_per_step / (ms / 1e3), 2), "unit": "views/s",
+                             "ms_per_view": round(ms / args.views_per_step, 4),
+                             "what": "rasterizer fwd+bwd + fused L1/SSIM loss per view + one Adam step over all parameters per "
+                                     "step (BASELINE config 3); timed with learning rate 0 so that the scene stays put",
+                             "checked_step": checked_adam_step(arm, lrs)}
+        out["ssim_ms"] = {"forward": round(kt.get("ssim_forward", {}).get("ms_per_view", 0.0), 4),
+                          "backward": round(kt.get("ssim_backward", {}).get("ms_per_view", 0.0), 4), "per": "1080p view, 3 channels"}
+        out["adam_ms"] = {"per_step": round(kt.get("adam_step", {}).get("ms_per_view", 0.0) * args.views_per_step, 4),
+                          "elements": 59 * args.gaussians}
+        del arm
+        torch.cuda.empty_cache()
+    except Exception as e:      # noqa: BLE001
+        out["train_step"] = {"error": repr(e)[:300]}
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import prof_densify as pdn
+        import gsr_densify as gd
+        p, mom, accum, denom = pdn.make(args.gaussians, dev)
+        rule = gd.make_rule(0.0002, 0.005, 5.0, 20, 0.01)
+        _, _, counts = gd.densify_raw(p, mom, accum, denom, rule)
+        noise = torch.randn(2 * counts[2], 3, device=dev)
+        ours = pdn.timed(lambda: gd.densify_raw(p, mom, accum, denom, rule, noise), 3)
+        ref = pdn.timed(lambda: pdn.torch_sequence(p, mom, accum, denom, 0.0002, 0.005, 5.0, 20, 0.01, noise), 3)
+        out["densify_ms"] = {"ours": round(ours, 3), "reference_op_sequence_in_torch": round(ref, 3),
+                             "points": args.gaussians, "points_after": counts[0] + counts[1] + 2 * counts[3]}
+        del p, mom, accum, denom, noise
+        torch.cuda.empty_cache()
+    except Exception as e:      # noqa: BLE001
+        out["densify_ms"] = {"error": repr(e)[:300]}
+    return out

@@ -4,7 +4,9 @@
 #include <cstdio>
 #include <cstring>
 #include <algorithm>
+#include <cstdlib>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -33,6 +35,21 @@ void prof_begin(const char* what, cudaStream_t s) {
 }
 void prof_end(cudaStream_t s) { cudaEventRecord(g_prof_recs.back().b, s); }
 
+int current_device(int* dev) { return (int)cudaGetDevice(dev); }
+int sm_count(int* sms) {
+    static int cache[kMaxDevices] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev >= 0 && dev < kMaxDevices && cache[dev] > 0) { *sms = cache[dev]; return 0; }
+    int n = 0;
+    e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev >= 0 && dev < kMaxDevices) cache[dev] = n;
+    *sms = n;
+    return 0;
+}
+
 int check_launch(const char* what, bool debug, cudaStream_t s) {
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess && debug) {            // auxiliary.h:166-173 (CHECK_CUDA in debug mode)
@@ -51,9 +68,9 @@ static size_t blob_size_geom(size_t P) {
     GeomState::from(p, P);
     return (size_t)p + GSR_ALIGN;
 }
-static size_t blob_size_binning(size_t R) {
+static size_t blob_size_binning(size_t R, size_t P, int W, int H) {
     char* p = nullptr;
-    BinningState::from(p, R);
+    BinningState::from(p, R, P, W, H);
     return (size_t)p + GSR_ALIGN;
 }
 static size_t blob_size_image(size_t N, size_t tiles) {
@@ -82,7 +99,9 @@ using namespace gsr;
 extern "C" {
 
 size_t gsr_required_geom(int P) { return blob_size_geom((size_t)(P > 0 ? P : 0)); }
-size_t gsr_required_binning(int R, int W, int H) { (void)W; (void)H; return blob_size_binning((size_t)(R > 0 ? R : 0)); }
+size_t gsr_required_binning(int R, int P, int W, int H) {
+    return blob_size_binning((size_t)(R > 0 ? R : 0), (size_t)(P > 0 ? P : 0), W > 0 ? W : 1, H > 0 ? H : 1);
+}
 size_t gsr_required_image(int W, int H) { return blob_size_image((size_t)W * H, (size_t)tiles_of(W, H)); }
 int gsr_key_bits(int W, int H) { return 32 + (int)higher_msb((uint32_t)tiles_of(W, H)); }
 size_t gsr_backward_scratch_bytes(int P) { return sizeof(float) * GSR_ACC_FLOATS * (size_t)(P > 0 ? P : 0) + 256; }
@@ -136,7 +155,7 @@ const char* gsr_error_string(int code) {
     switch (code) {
         case 0: return "ok";
         case GSR_E_BADARG: return "gsr: bad argument";
-        case GSR_E_TOOLARGE: return "gsr: num_rendered too large";
+        case GSR_E_TOOLARGE: return "gsr: too large (num_rendered >= 2^30 - 1, or more than 2^20 tiles)";
         case GSR_E_ALLOC: return "gsr: scratch allocation callback returned NULL";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "gsr: unknown error";
     }
@@ -152,13 +171,10 @@ int gsr_geom_layout(int P, size_t* off, int max_off) {
     return n;
 }
 int gsr_binning_layout(int R, int W, int H, size_t* off, int max_off) {
-    (void)W; (void)H;
-    char* p = nullptr;
-    BinningState b = BinningState::from(p, (size_t)R);
-    const size_t v[] = {(size_t)b.tile_keys, (size_t)b.point_list, (size_t)b.tile_keys_tmp, (size_t)b.vals_tmp};
-    int n = 0;
-    for (; n < 4 && n < max_off; n++) off[n] = v[n];
-    return n;
+    (void)R; (void)W; (void)H;                  // point_list sits at the blob's base whatever capacity it was sized for
+    if (max_off < 1) return 0;
+    off[0] = (size_t)BinningState::point_list_of(nullptr);
+    return 1;
 }
 int gsr_image_layout(int W, int H, size_t* off, int max_off) {
     char* p = nullptr;
@@ -167,6 +183,94 @@ int gsr_image_layout(int W, int H, size_t* off, int max_off) {
     int n = 0;
     for (; n < 3 && n < max_off; n++) off[n] = v[n];
     return n;
+}
+
+// ---- speculative capacity of the binning blob ------------------------------------------------------------------------
+// The reference stops the GPU in the middle of every forward: it copies num_rendered to the host, waits, sizes the
+// binning buffers and only then launches the remaining kernels (rasterizer_impl.cu:281-284). Here the host remembers,
+// per (device, image size), the largest instance count seen so far (relative to the number of Gaussians), sizes the blob
+// from that estimate, launches EVERYTHING, and waits for the count -- copied to pinned memory right after the emission
+// kernel -- only once the whole forward is queued: the GPU never idles. Every kernel reads the count from the device and
+// clamps its writes to the capacity; if the estimate was too small the later stages turn into no-ops and binning + blend
+// are repeated with a blob of the right size (then the estimate is raised). The first forward of a shape has no estimate
+// and takes the reference's route (count, wait, allocate). gsr_set_speculation(0) forces that route always.
+namespace {
+struct CapHint { int dev, W, H; double per_gaussian; double high; };
+std::mutex g_hint_mu;
+std::vector<CapHint> g_hints;
+int g_speculate = -1;                        // -1: read GSR_SPECULATE on first use
+unsigned long long g_spec_hits = 0, g_spec_retries = 0, g_spec_cold = 0;
+
+bool speculation_on() {
+    if (g_speculate < 0) {
+        const char* e = getenv("GSR_SPECULATE");
+        g_speculate = (e && e[0] == '0') ? 0 : 1;
+    }
+    return g_speculate != 0;
+}
+uint32_t hint_capacity(int dev, int W, int H, int P) {
+    std::lock_guard<std::mutex> lk(g_hint_mu);
+    for (auto& h : g_hints)
+        if (h.dev == dev && h.W == W && h.H == H) {
+            // the larger of: the largest count seen, and the largest count per Gaussian seen scaled to this P (a growing
+            // map raises the count with it); 1/8 headroom, rounded up to whole sort tiles
+            double c = std::max(h.high, h.per_gaussian * (double)P) * 1.125 + 8192.0;
+            if (c > 1.0e9) c = 1.0e9;
+            return (uint32_t)(((size_t)c + GSR_SORT_TILE - 1) / GSR_SORT_TILE * GSR_SORT_TILE);
+        }
+    return 0;
+}
+void hint_update(int dev, int W, int H, int P, uint32_t R) {
+    std::lock_guard<std::mutex> lk(g_hint_mu);
+    const double per = P > 0 ? (double)R / (double)P : 0.0;
+    for (auto& h : g_hints)
+        if (h.dev == dev && h.W == W && h.H == H) {
+            // slow decay, so that one outlier view does not pin the capacity for ever
+            h.high = std::max((double)R, h.high * 0.999);
+            h.per_gaussian = std::max(per, h.per_gaussian * 0.999);
+            return;
+        }
+    if (g_hints.size() >= 64) g_hints.erase(g_hints.begin());
+    g_hints.push_back(CapHint{dev, W, H, per, (double)R});
+}
+
+// pinned word + event for the count's way home (one per host thread: gsr_forward waits before it returns)
+struct CountSlot {
+    uint32_t* host = nullptr;
+    unsigned long long* host64 = nullptr;
+    cudaEvent_t ev[kMaxDevices] = {};
+    bool have[kMaxDevices] = {};
+    int get(int dev, cudaEvent_t* e) {
+        if (!host) {
+            void* p = nullptr;
+            cudaError_t ce = cudaHostAlloc(&p, 64, cudaHostAllocPortable);
+            if (ce != cudaSuccess) return (int)ce;
+            host = reinterpret_cast<uint32_t*>(p);
+            host64 = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(p) + 16);
+        }
+        if (dev < 0 || dev >= kMaxDevices) return GSR_E_BADARG;
+        if (!have[dev]) {                      // events belong to a device
+            cudaError_t ce = cudaEventCreateWithFlags(&ev[dev], cudaEventDisableTiming);
+            if (ce != cudaSuccess) return (int)ce;
+            have[dev] = true;
+        }
+        *e = ev[dev];
+        return 0;
+    }
+};
+thread_local CountSlot t_slot;
+}  // namespace
+
+int gsr_set_speculation(int on) { g_speculate = on ? 1 : 0; return 0; }
+int gsr_reset_capacity_hints(void) {
+    std::lock_guard<std::mutex> lk(g_hint_mu);
+    g_hints.clear();
+    return 0;
+}
+int gsr_speculation_stats(unsigned long long* out3) {
+    if (!out3) return GSR_E_BADARG;
+    out3[0] = g_spec_hits; out3[1] = g_spec_retries; out3[2] = g_spec_cold;
+    return 0;
 }
 
 int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, gsr_alloc_fn binning_alloc,
@@ -184,29 +288,73 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
         return (int)e;
     }
     if (!radii) return GSR_E_BADARG;
+    if ((long long)tiles > (1ll << 20)) return GSR_E_TOOLARGE;      // tile ids are sorted in at most 20 bits (16K x 16K pixels)
     char* gp = geom_alloc(geom_ctx, blob_size_geom((size_t)v.P));
     char* ip = image_alloc(image_ctx, blob_size_image(N, (size_t)tiles));
     if (!gp || !ip) return GSR_E_ALLOC;
     GeomState g = GeomState::from(gp, (size_t)v.P);
     ImageState img = ImageState::from(ip, N, (size_t)tiles);
 
-    int e = launch_preprocess(v, g, radii, s);
+    int dev = 0;
+    int e = current_device(&dev);
     if (e) return e;
-    uint32_t* total_dev = nullptr;
-    e = launch_order_and_scan(v, g, &total_dev, s);
+    cudaEvent_t ev;
+    e = t_slot.get(dev, &ev);
     if (e) return e;
-    uint32_t R = 0;   // rasterizer_impl.cu:281 : the one host synchronisation of the forward
-    cudaError_t ce = cudaMemcpyAsync(&R, total_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, s);
-    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
-    if (ce != cudaSuccess) return (int)ce;
-    if (R >= (1u << 30)) return GSR_E_TOOLARGE;
+    e = launch_preprocess(v, g, radii, s);
+    if (e) return e;
+    e = launch_depth_order(v, g, s);
+    if (e) return e;
+
+    constexpr uint32_t kLimit = (1u << 30) - 1u;                      // saturation value of the scan
+    uint32_t cap = speculation_on() ? hint_capacity(dev, v.W, v.H, v.P) : 0u;
+    uint32_t R = 0;
+    const bool cold = cap == 0u;
+    if (cold) {
+        // no estimate for this image size yet: count first (rasterizer_impl.cu:281, the reference's one host synchronisation)
+        g_spec_cold++;
+        e = launch_count_instances(v, g, s);
+        if (e) return e;
+        cudaError_t ce = cudaMemcpyAsync(t_slot.host64, g.count64, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+        if (ce != cudaSuccess) return (int)ce;
+        if (*t_slot.host64 >= (unsigned long long)kLimit) return GSR_E_TOOLARGE;
+        R = (uint32_t)*t_slot.host64;
+        cap = R;
+    }
+    if (cap >= kLimit) cap = kLimit - 1u;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        char* bp = binning_alloc(binning_ctx, blob_size_binning((size_t)cap, (size_t)v.P, v.W, v.H));
+        if (!bp) return GSR_E_ALLOC;
+        BinningState b = BinningState::from(bp, (size_t)cap, (size_t)v.P, v.W, v.H);
+        uint32_t* total_dev = nullptr;
+        e = launch_binning(v, g, radii, b, img, cap, &total_dev, s);
+        if (e) return e;
+        if (!cold || attempt > 0 || v.debug) {                        // the count goes home while the rest is being queued
+            cudaError_t ce = cudaMemcpyAsync(t_slot.host, total_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, s);
+            if (ce == cudaSuccess) ce = cudaEventRecord(ev, s);
+            if (ce != cudaSuccess) return (int)ce;
+        }
+        e = launch_blend_forward(v, g, b.point_list, img, out_color, out_invdepth, cold && attempt == 0 ? nullptr : total_dev, cap, s);
+        if (e) return e;
+        if (cold && attempt == 0 && !v.debug) break;                  // exact capacity: nothing to check
+        cudaError_t ce = cudaEventSynchronize(ev);                    // waits for the emission kernel only; the sort and the
+        if (ce != cudaSuccess) return (int)ce;                        // blend queued behind it keep the GPU busy
+        const uint32_t got = *t_slot.host;
+        if (cold && attempt == 0) {                                   // debug mode: the two counts must agree
+            if (got != R) return GSR_E_BADARG;
+            break;
+        }
+        if (got >= kLimit) return GSR_E_TOOLARGE;
+        R = got;
+        if (R <= cap) { if (attempt == 0) g_spec_hits++; break; }
+        if (attempt == 1) return GSR_E_BADARG;                        // cannot happen: the second blob has exactly R slots
+        g_spec_retries++;
+        cap = R;                                                      // the estimate was too small: once more, exact size
+    }
+    hint_update(dev, v.W, v.H, v.P, R);
     *num_rendered = (int)R;
-    char* bp = binning_alloc(binning_ctx, blob_size_binning((size_t)R));
-    if (!bp) return GSR_E_ALLOC;
-    BinningState b = BinningState::from(bp, (size_t)R);
-    e = launch_binning(v, g, radii, b, img, (int)R, s);
-    if (e) return e;
-    return launch_blend_forward(v, g, b, img, out_color, out_invdepth, s);
+    return 0;
 }
 
 int gsr_backward(const gsr_view* view, int R, const int* radii, const char* geom, const char* binning, const char* image,
@@ -224,18 +372,12 @@ int gsr_backward(const gsr_view* view, int R, const int* radii, const char* geom
     char* ip = const_cast<char*>(image);
     GeomState g = GeomState::from(gp, (size_t)v.P);
     ImageState img = ImageState::from(ip, (size_t)v.W * v.H, (size_t)tiles_of(v.W, v.H));
-    BinningState b;
-    memset(&b, 0, sizeof(b));
-    if (R > 0) {
-        char* bp = const_cast<char*>(binning);
-        b = BinningState::from(bp, (size_t)R);
-    }
     char* ap = accum_scratch;
     float* acc = carve<float>(ap, (size_t)v.P * GSR_ACC_FLOATS);
     GSR_MEMSET("memset_grad_acc", s, acc, 0, sizeof(float) * GSR_ACC_FLOATS * (size_t)v.P);
     int e = 0;
     if (R > 0) {
-        e = launch_blend_backward(v, g, b, img, dL_dpix, dL_dinvdepth, acc, s);
+        e = launch_blend_backward(v, g, BinningState::point_list_of(binning), img, dL_dpix, dL_dinvdepth, acc, s);
         if (e) return e;
     }
     gsr_grads o = *out;
@@ -260,14 +402,14 @@ int gsr_dist2(int P, const float* points_xyz, float* mean_d2, char* temp, void* 
 
 // Parity helper (not on the hot path): reconstruct the reference's sorted 64-bit keys
 // (tile << 32 | depth bits) for the instances of the last forward, for bit-exact comparison.
-int gsr_debug_sorted_keys(const gsr_view* view, int R, const char* geom, const char* binning, uint64_t* keys_out,
-                          void* stream) {
-    if (!view || !geom || !binning || !keys_out) return GSR_E_BADARG;
+int gsr_debug_sorted_keys(const gsr_view* view, int R, const char* geom, const char* binning, const char* image,
+                          uint64_t* keys_out, void* stream) {
+    if (!view || view->W <= 0 || view->H <= 0 || !geom || !binning || !image || !keys_out) return GSR_E_BADARG;
     char* gp = const_cast<char*>(geom);
-    char* bp = const_cast<char*>(binning);
+    char* ip = const_cast<char*>(image);
     GeomState g = GeomState::from(gp, (size_t)view->P);
-    BinningState b = BinningState::from(bp, (size_t)R);
-    return launch_sorted_keys_debug(*view, g, b, R, keys_out, (cudaStream_t)stream);
+    ImageState img = ImageState::from(ip, (size_t)view->W * view->H, (size_t)tiles_of(view->W, view->H));
+    return launch_sorted_keys_debug(*view, g, BinningState::point_list_of(binning), img, R, keys_out, (cudaStream_t)stream);
 }
 
 int gsr_ssim_forward(int B, int CH, int H, int W, float C1, float C2, const float* img1, const float* img2,
@@ -408,17 +550,21 @@ int gsr_debug_blend_stats(const gsr_view* view, int R, const char* geom, const c
     if (R <= 0 || view->P <= 0) return 0;
     if (!binning) return GSR_E_BADARG;
     char* gp = const_cast<char*>(geom);
-    char* bp = const_cast<char*>(binning);
     char* ip = const_cast<char*>(image);
     GeomState g = GeomState::from(gp, (size_t)view->P);
-    BinningState b = BinningState::from(bp, (size_t)R);
+    const uint32_t* point_list = BinningState::point_list_of(binning);
     ImageState img = ImageState::from(ip, (size_t)view->W * view->H, (size_t)tiles_of(view->W, view->H));
-    int e = launch_blend_stats(*view, g, b, img, counts_dev, (cudaStream_t)stream);
+    int e = launch_blend_stats(*view, g, point_list, img, counts_dev, (cudaStream_t)stream);
     if (e) return e;
-    return launch_cull_stats(*view, g, b, img, counts_dev, (cudaStream_t)stream);
+    return launch_cull_stats(*view, g, point_list, img, counts_dev, (cudaStream_t)stream);
 }
 
 int gsr_debug_set_exact_cull(int on) { return set_exact_cull(on); }
+
+int gsr_debug_fp32_peak(int iters, float* out, int* sms_out, void* stream) {
+    if (iters <= 0 || !out) return GSR_E_BADARG;
+    return launch_fp32_peak(iters, out, sms_out, (cudaStream_t)stream);
+}
 
 int gsr_debug_exp_mismatches(unsigned long long* mismatches_dev, void* stream) {
     if (!mismatches_dev) return GSR_E_BADARG;

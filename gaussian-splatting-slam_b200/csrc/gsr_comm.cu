@@ -223,13 +223,8 @@ int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas,
     const long long n16 = numel / 4;
     comm_slice(n16, g.rank, g.world, &a.lo, &a.hi);
     // the grid must be the same on every rank (CTAs meet their twins): derive it from the largest slice only
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaError_t e = cudaGetDevice(&dev);
-        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e != cudaSuccess) return (int)e;
-    }
+    int sms = 0;
+    { const int e = sm_count(&sms); if (e) return e; }
     const long long per = (n16 + g.world - 1) / g.world;
     long long ctas = (per + (long long)kCommThreads * kCommUnroll - 1) / ((long long)kCommThreads * kCommUnroll);
     long long cap = max_ctas > 0 ? max_ctas : 2 * sms;
@@ -275,13 +270,8 @@ int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& para
         a.inv_sqrt_bc2[k] = k < n_spans ? spans[k].inv_sqrt_bc2 : 0.f;
     }
     a.h = AdamHyper{(float)(1.0 - b1), (float)b2, (float)(1.0 - b2), (float)eps};
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        cudaError_t e = cudaGetDevice(&dev);
-        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e != cudaSuccess) return (int)e;
-    }
+    int sms = 0;
+    { const int e = sm_count(&sms); if (e) return e; }
     const long long per = (n16 + grads.world - 1) / grads.world;
     long long ctas = (per + (long long)kCommThreads * 2 - 1) / ((long long)kCommThreads * 2);
     long long cap = max_ctas > 0 ? max_ctas : 2 * sms;

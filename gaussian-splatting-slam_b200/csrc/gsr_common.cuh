@@ -34,6 +34,26 @@ void prof_end(cudaStream_t s);
         if (_ce != cudaSuccess) return (int)_ce;                                   \
     } while (0)
 
+// ---------------------------------------------------------------- per-device launch state
+// Function attributes (opt-in dynamic shared memory) and the SM count belong to a DEVICE, not to the process: a
+// caller may render on cuda:0 and then on cuda:1 (the binding follows the tensors' device). DeviceOnce remembers, per
+// kernel, on which devices the attribute has been set; sm_count() caches cudaDevAttrMultiProcessorCount per device.
+constexpr int kMaxDevices = 64;
+struct DeviceOnce { bool done[kMaxDevices] = {}; };
+int current_device(int* dev);                        // cudaGetDevice with error code
+int sm_count(int* sms);                              // SMs of the current device (cached per device)
+template <typename F>
+static inline int ensure_dynamic_smem(F* kernel, int bytes, DeviceOnce& once) {
+    int dev = 0;
+    int e = current_device(&dev);
+    if (e) return e;
+    if (dev >= 0 && dev < kMaxDevices && once.done[dev]) return 0;
+    cudaError_t ce = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (ce != cudaSuccess) return (int)ce;
+    if (dev >= 0 && dev < kMaxDevices) once.done[dev] = true;
+    return 0;
+}
+
 // ---------------------------------------------------------------- Adam update (shared by gsr_adam.cu and gsr_comm.cu)
 struct AdamHyper { float omb1, b2, omb2, eps; };      // 1 - beta1, beta2, 1 - beta2 (rounded from double, as torch does), eps
 #ifdef __CUDACC__
@@ -81,10 +101,9 @@ struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46
     uint32_t* order;          // [P] Gaussian ids in (depth, id) order
     uint32_t* order_tmp;      // [P]
     uint32_t* point_offsets;  // [P] inclusive scan of tiles_touched[order[j]]  (depth order!)
-    uint32_t* scan_sums;      // [scan tiles + 8]; last word = total (num_rendered)
     uint32_t* sort_scratch;   // radix-sort tables for the P-sized sort
+    unsigned long long* count64;  // [2] instance count of the view (only written when the forward has no capacity estimate)
     uint32_t* rect_packed;    // [P] tile rectangle x0 | y0 << 8 | width << 16 | height << 24 (visible Gaussians; grids up to 255 x 255 tiles)
-    uint32_t* rect_sorted;    // [P] the same words in depth order (written by the scan, read by the instance emission)
     uint32_t* n_visible;      // [1] Gaussians that survived the cull = valid prefix of order / point_offsets (device)
     static GeomState from(char*& p, size_t P) {
         GeomState g;
@@ -97,10 +116,9 @@ struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46
         g.order = carve<uint32_t>(p, P);
         g.order_tmp = carve<uint32_t>(p, P);
         g.point_offsets = carve<uint32_t>(p, P);
-        g.scan_sums = carve<uint32_t>(p, (P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE + 8);
         g.sort_scratch = carve<uint32_t>(p, sort_scratch_words(P));
+        g.count64 = carve<unsigned long long>(p, 2);
         g.rect_packed = carve<uint32_t>(p, P);
-        g.rect_sorted = carve<uint32_t>(p, P);
         g.n_visible = g.sort_scratch + 4 * GSR_RADIX + 8;      // where radix_sort_u32's drop mode leaves the kept count
         return g;
     }
@@ -120,20 +138,40 @@ struct ImageState {           // replaces ImageState (rasterizer_impl.h:48-55)
 };
 
 struct BinningState {         // replaces BinningState (rasterizer_impl.h:57-66)
-    uint32_t* tile_keys;      // [R] tile id per instance, sorted (final)
+    // R below is the CAPACITY the blob was sized for (>= num_rendered: the speculative forward sizes it before the count
+    // is known). point_list comes first, so consumers of a finished forward (backward, statistics) find it without
+    // knowing that capacity; everything behind it is private to the forward.
     uint32_t* point_list;     // [R] Gaussian ids sorted by (tile, depth, id) (final)
+    uint32_t* tile_keys;      // [R] tile id per instance (ping-pong partner of tile_keys_tmp; not kept sorted)
     uint32_t* tile_keys_tmp;  // [R]
     uint32_t* vals_tmp;       // [R]
-    uint32_t* sort_scratch;   // radix-sort tables for the R-sized sort
-    static BinningState from(char*& p, size_t R) {
+    uint32_t* sort_scratch;   // radix-sort tables for the R-sized sort: digit histograms [4][256], tickets, look-back status
+    uint32_t* scan_sums;      // [scan tiles + 8]: look-back words of the tile-count scan, then total (num_rendered), ticket
+    int32_t* tile_diff;       // [(gx + 1) * (gy + 1)] difference array of the tile rectangles (+1 / -1 at the corners); its
+                              // 2-D prefix sum is the number of instances per tile (tile table: ranges, digit histograms)
+    char* zero_begin;         // [zero_begin, zero_end): what one memset clears before every binning (tickets, status words,
+    char* zero_end;           // scan words, difference array); the histograms in front of it are overwritten
+    static size_t diff_cells(int W, int H) {
+        return (size_t)((W + GSR_TILE - 1) / GSR_TILE + 1) * (size_t)((H + GSR_TILE - 1) / GSR_TILE + 1);
+    }
+    static size_t scan_tiles(size_t P) { return (P + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE; }
+    static BinningState from(char*& p, size_t R, size_t P, int W, int H) {
         BinningState b;
         size_t Rp = R + 8;
-        b.tile_keys = carve<uint32_t>(p, Rp);
         b.point_list = carve<uint32_t>(p, Rp);
+        b.tile_keys = carve<uint32_t>(p, Rp);
         b.tile_keys_tmp = carve<uint32_t>(p, Rp);
         b.vals_tmp = carve<uint32_t>(p, Rp);
         b.sort_scratch = carve<uint32_t>(p, sort_scratch_words(R));
+        b.scan_sums = carve<uint32_t>(p, scan_tiles(P) + 8);
+        b.tile_diff = carve<int32_t>(p, diff_cells(W, H));
+        b.zero_begin = reinterpret_cast<char*>(b.sort_scratch + 4 * GSR_RADIX);
+        b.zero_end = reinterpret_cast<char*>(b.tile_diff + diff_cells(W, H));
         return b;
+    }
+    static const uint32_t* point_list_of(const char* blob) {      // all a finished forward's consumers need
+        char* p = const_cast<char*>(blob);
+        return carve<uint32_t>(p, 0);
     }
 };
 
@@ -156,25 +194,37 @@ static inline uint32_t higher_msb(uint32_t n) {   // rasterizer_impl.cu:35-50
 // ---------------------------------------------------------------- stage entry points (host)
 int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s);
-// depth-order the Gaussians, scan their tile counts in that order; total lands in g.scan_sums (device)
-int launch_order_and_scan(const gsr_view& v, GeomState& g, uint32_t** total_dev, cudaStream_t s);
-int launch_binning(const gsr_view& v, const GeomState& g, const int* radii, BinningState& b, ImageState& img,
-                   int R, cudaStream_t s);
-int launch_blend_forward(const gsr_view& v, const GeomState& g, const BinningState& b, ImageState& img,
-                         float* out_color, float* out_invdepth, cudaStream_t s);
-int launch_blend_backward(const gsr_view& v, const GeomState& g, const BinningState& b, const ImageState& img,
+// depth-order the visible Gaussians (drop-mode radix sort; the visible count stays on the device)
+int launch_depth_order(const gsr_view& v, GeomState& g, cudaStream_t s);
+// number of instances = sum of the tile counts (only used when the forward has no capacity estimate yet); *total_dev
+// points at the device word
+int launch_count_instances(const gsr_view& v, GeomState& g, cudaStream_t s);
+// scan of the tile counts in depth order + instance emission (one kernel), tile table (ranges + digit histograms from the
+// rectangles' difference array), stable sort by tile id. `cap` = instances the binning blob holds; the real count lands
+// in *total_dev (device). Safe for any count: writes are clamped to cap, and a count above cap turns the later stages
+// (sort passes, forward blend) into no-ops so that the caller can repeat the call with a larger blob.
+int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img,
+                   uint32_t cap, uint32_t** total_dev, cudaStream_t s);
+int launch_blend_forward(const gsr_view& v, const GeomState& g, const uint32_t* point_list, ImageState& img,
+                         float* out_color, float* out_invdepth, const uint32_t* total_dev, uint32_t cap, cudaStream_t s);
+int launch_blend_backward(const gsr_view& v, const GeomState& g, const uint32_t* point_list, const ImageState& img,
                           const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s);
 int launch_preprocess_backward(const gsr_view& v, const GeomState& g, const int* radii, const float* acc,
                                bool have_invdepth, const gsr_grads& out, cudaStream_t s);
 // Stable LSD radix sort of (u32 key, u32 value) pairs on key bits [0, total_bits). Ping-pongs between
 // (ka,va) and (kb,vb); *result_in_a tells where the sorted data ended up. scratch: sort_scratch_words(n).
+struct SortOptions {
+    bool hist_ready;          // the digit histograms are already in scratch[0 .. passes * 256): no histogram kernel
+    const uint32_t* n_dev;    // device word holding the real pair count (then n is only the capacity), or NULL
+    bool values_only_last;    // the last pass writes no keys
+};
 int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits,
                    uint32_t* scratch, bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev = nullptr,
-                   bool scratch_zeroed = false);
+                   bool scratch_zeroed = false, const SortOptions* opt = nullptr);
 static inline int radix_passes(int total_bits) { return (total_bits + 7) / 8; }
-int launch_sorted_keys_debug(const gsr_view& v, const GeomState& g, const BinningState& b, int R, uint64_t* keys_out,
-                             cudaStream_t s);
-int launch_blend_stats(const gsr_view& v, const GeomState& g, const BinningState& b, const ImageState& img,
+int launch_sorted_keys_debug(const gsr_view& v, const GeomState& g, const uint32_t* point_list, const ImageState& img, int R,
+                             uint64_t* keys_out, cudaStream_t s);
+int launch_blend_stats(const gsr_view& v, const GeomState& g, const uint32_t* point_list, const ImageState& img,
                        unsigned long long* out, cudaStream_t s);
 int launch_ssim_forward(int planes, int H, int W, float C1, float C2, const float* img1, const float* img2, float* ssim_map,
                         float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12, double* sums, cudaStream_t s);
@@ -190,7 +240,7 @@ int launch_densify_apply(int P, const void* blob, const gsr_densify_rule* rule, 
 int launch_densify_stats(int P, const float* dL_dmean2D, const uint8_t* update_filter, const int* radii, float* grad_accum,
                          float* denom, float* max_radii2D, cudaStream_t s);
 int set_exact_cull(int on);
-int launch_cull_stats(const gsr_view& v, const GeomState& g, const BinningState& b, const ImageState& img,
+int launch_cull_stats(const gsr_view& v, const GeomState& g, const uint32_t* point_list, const ImageState& img,
                       unsigned long long* out, cudaStream_t s);
 int launch_adam(const gsr_adam_group* groups, int n, double b1, double b2, double eps, const uint8_t* visible, cudaStream_t s);
 int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& params, float* exp_avg, float* exp_avg_sq,
@@ -199,6 +249,7 @@ int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& para
 int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas, cudaStream_t s);
 void comm_slice(long long n16, int rank, int world, long long* lo, long long* hi);
 int launch_exp_check(unsigned long long* mismatches_dev, cudaStream_t s);
+int launch_fp32_peak(int iters, float* out, int* sms_out, cudaStream_t s);
 int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s);
 size_t dist2_temp_bytes(int P);
 

@@ -769,12 +769,8 @@ int launch_preprocess_backward(const gsr_view& v, const GeomState& g, const int*
     const bool fast = sh16_fast(v) && out.dL_dsh != nullptr && (reinterpret_cast<uintptr_t>(out.dL_dsh) & 15) == 0;
     if (fast) {
         const int smem = 256 * kShRow * (int)sizeof(float);
-        static bool attr_set = false;                 // one process drives one device
-        if (!attr_set) {
-            cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-            if (e != cudaSuccess) return (int)e;
-            attr_set = true;
-        }
+        static DeviceOnce once;                       // the opt-in is per device
+        { const int e = ensure_dynamic_smem(preprocess_bwd_kernel<true>, smem, once); if (e) return e; }
         GSR_LAUNCH("preprocess_bwd", v.debug, s, (preprocess_bwd_kernel<true><<<blocks, 256, smem, s>>>(b)));
     }
     else

@@ -153,7 +153,7 @@ __device__ __forceinline__ void sort_prefetch(SortSmem& sm, const uint32_t* __re
 }
 
 // ranks, publishes, reorders and writes out one tile whose pairs are already in registers
-template <int BITS, bool FULL, bool DROP>
+template <int BITS, bool FULL, bool DROP, bool WRITE_KEYS>
 __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key)[kSortItems], const uint32_t (&val)[kSortItems],
                                               uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n,
                                               int shift, int tile, uint32_t gbase, uint32_t* __restrict__ status) {
@@ -234,7 +234,7 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
         if ((FULL && !DROP) || slot < count_out) {
             const uint32_t k = sm.s_keys[slot];
             const uint32_t pos = sm.gofs[(k >> shift) & mask] + (uint32_t)slot;
-            keys_out[pos] = k;
+            if (WRITE_KEYS) keys_out[pos] = k;
             vals_out[pos] = sm.s_vals[slot];
         }
     }
@@ -243,7 +243,12 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
 // MODE 0: plain pass. MODE 1 ("drop"): pairs whose key is 0xFFFFFFFF are left out of the output (the histograms do not
 // count them either), so the pass also compacts; the number of kept pairs goes to *n_valid_out. MODE 2: a pass after a
 // drop pass -- the pair count is not known to the host, it is the total of this pass's own histogram.
-template <int BITS, int MODE>
+// n_dev != NULL: the pair count lives on the device (the instance sort of the speculative forward: the host sizes the
+// launch for the capacity `n` of the buffers and learns the real count later). A count above the capacity means the
+// buffers were too small: the pass does nothing (the caller repeats the binning with larger ones).
+// WRITE_KEYS = false: the last pass of the instance sort leaves the keys unwritten (nobody reads sorted tile ids: the
+// tile ranges come from the tile table).
+template <int BITS, int MODE, bool WRITE_KEYS>
 __global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_t* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     uint32_t* __restrict__ keys_out,
@@ -251,10 +256,17 @@ __global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_
                                                                     int shift, const uint32_t* __restrict__ ghist,
                                                                     uint32_t* __restrict__ ticket,
                                                                     uint32_t* __restrict__ status,
-                                                                    uint32_t* __restrict__ n_valid_out) {
+                                                                    uint32_t* __restrict__ n_valid_out,
+                                                                    const uint32_t* __restrict__ n_dev) {
     extern __shared__ __align__(16) unsigned char sort_smem_raw[];
     SortSmem& sm = *reinterpret_cast<SortSmem*>(sort_smem_raw);
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    if (MODE == 0 && n_dev != nullptr) {
+        const uint32_t nd = __ldg(n_dev);
+        if (nd > (uint32_t)n) return;                      // overflow of the speculative capacity: uniform over the grid
+        n = (int)nd;
+        n_tiles = (n + GSR_SORT_TILE - 1) / GSR_SORT_TILE;
+    }
     if (t == 0) sm.tile = atomicAdd(ticket, 1u);
     const uint32_t hcount = __ldg(ghist + t);
     const uint32_t gbase = block_excl_scan256(hcount, sm.warp_sums);   // first output slot of digit t (syncs)
@@ -284,37 +296,56 @@ __global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_
         __syncthreads();                                   // everybody holds its pairs: the prefetch buffers are free again
         if (next < n_tiles) sort_prefetch(sm, keys_in, vals_in, n, next);
         if ((tile + 1) * GSR_SORT_TILE <= n)
-            onesweep_tile<BITS, true, MODE == 1>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
+            onesweep_tile<BITS, true, MODE == 1, WRITE_KEYS>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
         else
-            onesweep_tile<BITS, false, MODE == 1>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
+            onesweep_tile<BITS, false, MODE == 1, WRITE_KEYS>(sm, key, val, keys_out, vals_out, n, shift, tile, gbase, status);
         if (next >= n_tiles) break;
         tile = next;
         __syncthreads();                                   // reorder buffers / gofs are read until here
     }
 }
 
-template <int BITS, int MODE = 0>
+template <int BITS, int MODE = 0, bool WRITE_KEYS = true>
 static int launch_pass(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, int n, int shift,
                        const uint32_t* ghist, uint32_t* ticket, uint32_t* status, int tiles, cudaStream_t s,
-                       uint32_t* n_valid_out = nullptr) {
-    static bool attr_set = false;                          // one process drives one device
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(onesweep_kernel<BITS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem));
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
-    }
-    const int ctas = tiles < 148 * 3 ? tiles : 148 * 3;
-    onesweep_kernel<BITS, MODE><<<ctas, kSortThreads, sizeof(SortSmem), s>>>(kin, vin, kout, vout, n, tiles, shift, ghist, ticket, status, n_valid_out);
+                       uint32_t* n_valid_out = nullptr, const uint32_t* n_dev = nullptr) {
+    static DeviceOnce once;                                // the opt-in is per device
+    int e = ensure_dynamic_smem(onesweep_kernel<BITS, MODE, WRITE_KEYS>, (int)sizeof(SortSmem), once);
+    if (e) return e;
+    int sms = 148;
+    e = sm_count(&sms);
+    if (e) return e;
+    const int ctas = tiles < sms * 3 ? tiles : sms * 3;
+    onesweep_kernel<BITS, MODE, WRITE_KEYS><<<ctas, kSortThreads, sizeof(SortSmem), s>>>(kin, vin, kout, vout, n, tiles, shift, ghist, ticket, status, n_valid_out, n_dev);
     return 0;
 }
 
+template <bool WRITE_KEYS>
+static int launch_pass_bits(int bits, const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, int n, int shift,
+                            const uint32_t* gh, uint32_t* ticket, uint32_t* st, int tiles, cudaStream_t s, const uint32_t* n_dev) {
+    switch (bits) {
+        case 1: return launch_pass<1, 0, WRITE_KEYS>(kin, vin, kout, vout, n, shift, gh, ticket, st, tiles, s, nullptr, n_dev);
+        case 2: return launch_pass<2, 0, WRITE_KEYS>(kin, vin, kout, vout, n, shift, gh, ticket, st, tiles, s, nullptr, n_dev);
+        case 3: return launch_pass<3, 0, WRITE_KEYS>(kin, vin, kout, vout, n, shift, gh, ticket, st, tiles, s, nullptr, n_dev);
+        case 4: return launch_pass<4, 0, WRITE_KEYS>(kin, vin, kout, vout, n, shift, gh, ticket, st, tiles, s, nullptr, n_dev);
+        case 5: return launch_pass<5, 0, WRITE_KEYS>(kin, vin, kout, vout, n, shift, gh, ticket, st, tiles, s, nullptr, n_dev);
+        case 6: return launch_pass<6, 0, WRITE_KEYS>(kin, vin, kout, vout, n, shift, gh, ticket, st, tiles, s, nullptr, n_dev);
+        case 7: return launch_pass<7, 0, WRITE_KEYS>(kin, vin, kout, vout, n, shift, gh, ticket, st, tiles, s, nullptr, n_dev);
+        default: return launch_pass<8, 0, WRITE_KEYS>(kin, vin, kout, vout, n, shift, gh, ticket, st, tiles, s, nullptr, n_dev);
+    }
+}
+
 int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits, uint32_t* scratch,
-                   bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev, bool scratch_zeroed) {
+                   bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev, bool scratch_zeroed,
+                   const SortOptions* opt) {
     // n_valid_dev != NULL ("drop" sort, 32-bit keys only): pairs whose key is 0xFFFFFFFF are not part of the result;
     // the first pass compacts them away, the later passes run over the kept pairs only, and *n_valid_dev points at
     // their count (device). The tail of the output arrays beyond that count is unspecified.
+    // opt (instance sort): hist_ready = the digit histograms in scratch[0 .. passes*256) were filled by the caller (the
+    // tile table) and no histogram kernel runs; n_dev = device word with the real pair count (n is the capacity);
+    // values_only_last = the last pass writes no keys.
     const bool drop = n_valid_dev != nullptr;
-    if (drop && total_bits != 32) return GSR_E_BADARG;
+    if (drop && (total_bits != 32 || opt != nullptr)) return GSR_E_BADARG;
     *result_in_a = true;
     if (drop) *n_valid_dev = scratch + 4 * GSR_RADIX + 8;          // a spare word of the ticket block (zeroed below)
     if (n <= 0 || total_bits <= 0) return 0;
@@ -323,33 +354,35 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
     uint32_t* ghist = scratch;                                  // [4][256]
     uint32_t* tickets = scratch + 4 * GSR_RADIX;                // [4] (+ padding)
     uint32_t* status = scratch + 4 * GSR_RADIX + 64;            // [passes][tiles][256]
-    if (!scratch_zeroed)
-        GSR_MEMSET("memset_sort", s, scratch, 0, sizeof(uint32_t) * (4 * GSR_RADIX + 64 + (size_t)passes * tiles * GSR_RADIX));
-    // a CTA pays a fixed price (clearing 32 KB of counters, flushing up to 1024 of them with global atomics), so it should
-    // see at least ~16K keys; 4 CTAs per SM at most
-    const int hist_blocks = min((n + 16383) / 16384, 148 * 4);
-    GSR_LAUNCH("radix_hist", debug, s,
-               (radix_hist_kernel<<<hist_blocks > 0 ? hist_blocks : 1, kSortThreads, 0, s>>>(ka, n, passes, total_bits, ghist, drop ? 1 : 0)));
+    const bool hist_ready = opt && opt->hist_ready;
+    const uint32_t* n_dev = opt ? opt->n_dev : nullptr;
+    if (!scratch_zeroed) {
+        // with the histograms already in place only the tickets and the look-back status are cleared
+        uint32_t* from = hist_ready ? tickets : scratch;
+        GSR_MEMSET("memset_sort", s, from, 0, sizeof(uint32_t) * ((size_t)(scratch + 4 * GSR_RADIX + 64 - from) + (size_t)passes * tiles * GSR_RADIX));
+    }
+    if (!hist_ready) {
+        // a CTA pays a fixed price (clearing 32 KB of counters, flushing up to 1024 of them with global atomics), so it
+        // should see at least ~16K keys; 4 CTAs per SM at most
+        int sms = 148;
+        { const int se = sm_count(&sms); if (se) return se; }
+        const int hist_blocks = min((n + 16383) / 16384, sms * 4);
+        GSR_LAUNCH("radix_hist", debug, s,
+                   (radix_hist_kernel<<<hist_blocks > 0 ? hist_blocks : 1, kSortThreads, 0, s>>>(ka, n, passes, total_bits, ghist, drop ? 1 : 0)));
+    }
     uint32_t *kin = ka, *vin = va, *kout = kb, *vout = vb;
     for (int p = 0; p < passes; p++) {
         const int shift = 8 * p;
         const int bits = (total_bits - shift) < 8 ? (total_bits - shift) : 8;
         uint32_t* st = status + (size_t)p * tiles * GSR_RADIX;
         const uint32_t* gh = ghist + p * GSR_RADIX;
+        const bool no_keys = opt && opt->values_only_last && p == passes - 1;
         int le = 0;
-        GSR_LAUNCH("onesweep_pass", debug, s, {
+        GSR_LAUNCH(drop ? "onesweep_depth" : (opt ? "onesweep_tile" : "onesweep_pass"), debug, s, {
             if (drop && p == 0) le = launch_pass<8, 1>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s, *n_valid_dev);
             else if (drop) le = launch_pass<8, 2>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s);
-            else switch (bits) {
-                case 1: le = launch_pass<1>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 2: le = launch_pass<2>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 3: le = launch_pass<3>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 4: le = launch_pass<4>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 5: le = launch_pass<5>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 6: le = launch_pass<6>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                case 7: le = launch_pass<7>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-                default: le = launch_pass<8>(kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s); break;
-            }
+            else if (no_keys) le = launch_pass_bits<false>(bits, kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s, n_dev);
+            else le = launch_pass_bits<true>(bits, kin, vin, kout, vout, n, shift, gh, tickets + p, st, tiles, s, n_dev);
         });
         if (le) return le;
         uint32_t* tk = kin; kin = kout; kout = tk;

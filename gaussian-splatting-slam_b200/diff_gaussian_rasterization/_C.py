@@ -54,10 +54,18 @@ def lib():
         L.gsr_debug_exp_mismatches.restype = C.c_int
         L.gsr_debug_exp_mismatches.argtypes = [C.c_void_p, C.c_void_p]
         L.gsr_debug_sorted_keys.restype = C.c_int
-        L.gsr_debug_sorted_keys.argtypes = [C.POINTER(_View), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.gsr_debug_sorted_keys.argtypes = [C.POINTER(_View), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.gsr_set_speculation.restype = C.c_int
+        L.gsr_set_speculation.argtypes = [C.c_int]
+        L.gsr_reset_capacity_hints.restype = C.c_int
+        L.gsr_speculation_stats.restype = C.c_int
+        L.gsr_speculation_stats.argtypes = [C.POINTER(C.c_ulonglong)]
+        L.gsr_debug_fp32_peak.restype = C.c_int
+        L.gsr_debug_fp32_peak.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_int), C.c_void_p]
         for n in ("gsr_required_geom", "gsr_required_image", "gsr_backward_scratch_bytes", "gsr_dist2_temp_bytes"):
             getattr(L, n).restype = C.c_size_t
         L.gsr_required_binning.restype = C.c_size_t
+        L.gsr_required_binning.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
         L.gsr_launch_count.restype = C.c_uint64
         L.gsr_profile_enable.restype = C.c_int
         L.gsr_profile_enable.argtypes = [C.c_int]
@@ -388,23 +396,60 @@ def decode_state(P, R, W, H, geomBuffer, binningBuffer, imgBuffer, view_args=Non
     if R > 0:
         n = L.gsr_binning_layout(C.c_int(R), C.c_int(W), C.c_int(H), off, 8)
         bo = [off[i] for i in range(n)]
-        out["tile_keys"] = take(binningBuffer, bo[0], 4 * R, torch.int32, (R,))
-        out["point_list"] = take(binningBuffer, bo[1], 4 * R, torch.int32, (R,))
+        out["point_list"] = take(binningBuffer, bo[0], 4 * R, torch.int32, (R,))
     return out
 
 
-def sorted_keys(P, R, geomBuffer, binningBuffer):
-    """Parity helper: the reference's sorted u64 keys (as int64) for the last forward."""
+def sorted_keys(P, R, W, H, geomBuffer, binningBuffer, imgBuffer):
+    """Parity helper: the reference's sorted u64 keys (as int64) for the last forward (tile id from the ranges the
+    instance falls into, depth bits of its Gaussian)."""
     dev = geomBuffer.device
     keys = torch.empty((R,), dtype=torch.int64, device=dev)
     if R > 0:
         view = _View()
-        view.P = P
+        view.P, view.W, view.H = P, W, H
         with torch.cuda.device(dev):
             _check(lib().gsr_debug_sorted_keys(C.byref(view), R, geomBuffer.data_ptr(), binningBuffer.data_ptr(),
-                                               keys.data_ptr(), torch.cuda.current_stream(dev).cuda_stream),
-                   "gsr_debug_sorted_keys")
+                                               imgBuffer.data_ptr(), keys.data_ptr(),
+                                               torch.cuda.current_stream(dev).cuda_stream), "gsr_debug_sorted_keys")
     return keys
+
+
+def set_speculation(on):
+    """gsr_set_speculation: False = size the binning blob from the counted num_rendered (one mid-forward sync, the
+    reference's route); True (default) = size it from the largest count seen for this image size."""
+    _check(lib().gsr_set_speculation(1 if on else 0), "gsr_set_speculation")
+
+
+def reset_capacity_hints():
+    _check(lib().gsr_reset_capacity_hints(), "gsr_reset_capacity_hints")
+
+
+def speculation_stats():
+    """(forwards whose capacity estimate held, forwards that repeated binning + blend, forwards that counted first)"""
+    out = (C.c_ulonglong * 3)()
+    _check(lib().gsr_speculation_stats(out), "gsr_speculation_stats")
+    return int(out[0]), int(out[1]), int(out[2])
+
+
+def fp32_peak_tflops(device="cuda", iters=4000, reps=5):
+    """Measured FP32 SIMT ceiling of the device (gsr_debug_fp32_peak, timed with CUDA events; best of reps)."""
+    dev = torch.device(device)
+    with torch.cuda.device(dev):
+        sms = C.c_int(0)
+        out = torch.empty(256 * 8 * 256, dtype=torch.float32, device=dev)       # up to 256 SMs
+        st = torch.cuda.current_stream(dev).cuda_stream
+        best = None
+        for _ in range(reps + 1):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _check(lib().gsr_debug_fp32_peak(iters, out.data_ptr(), C.byref(sms), st), "gsr_debug_fp32_peak")
+            e1.record()
+            e1.synchronize()
+            ms = e0.elapsed_time(e1)
+            best = ms if best is None else min(best, ms)
+        flop = 2.0 * 16 * iters * 256 * 8 * sms.value
+    return flop / (best * 1e-3) / 1e12
 
 
 def exp_mismatches(device="cuda"):

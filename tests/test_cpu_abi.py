@@ -56,8 +56,19 @@ def test_host_helpers(gsr_lib):
         small = f(*[C.c_int(a) for a in args])
         big = f(*[C.c_int(a * 2) for a in args])
         assert 0 < small < big
-    assert L.gsr_required_binning(C.c_int(0), C.c_int(64), C.c_int(64)) > 0
-    assert L.gsr_required_binning(C.c_int(10 ** 6), C.c_int(64), C.c_int(64)) >= 16 * 10 ** 6
+    assert L.gsr_required_binning(C.c_int(0), C.c_int(100), C.c_int(64), C.c_int(64)) > 0
+    assert L.gsr_required_binning(C.c_int(10 ** 6), C.c_int(1000), C.c_int(64), C.c_int(64)) >= 16 * 10 ** 6
+    # the binning blob also holds the scan words (P) and the tile table's difference array (W, H)
+    assert L.gsr_required_binning(C.c_int(4096), C.c_int(10 ** 6), C.c_int(64), C.c_int(64)) > \
+        L.gsr_required_binning(C.c_int(4096), C.c_int(1000), C.c_int(64), C.c_int(64))
+    assert L.gsr_required_binning(C.c_int(4096), C.c_int(1000), C.c_int(1920), C.c_int(1080)) > \
+        L.gsr_required_binning(C.c_int(4096), C.c_int(1000), C.c_int(64), C.c_int(64))
+    # point_list sits at the blob's base whatever the capacity
+    boff = (C.c_size_t * 8)()
+    assert L.gsr_binning_layout(C.c_int(12345), C.c_int(64), C.c_int(64), boff, 8) == 1 and boff[0] == 0
+    assert L.gsr_set_speculation(1) == 0 and L.gsr_reset_capacity_hints() == 0
+    st3 = (C.c_ulonglong * 3)()
+    assert L.gsr_speculation_stats(st3) == 0
     assert L.gsr_error_string(0) == b"ok"
     assert b"bad argument" in L.gsr_error_string(-1)
     assert b"sm_100a" in L.gsr_version()

@@ -7,7 +7,7 @@ import torch, bench
 sys.argv = [sys.argv[0], "--views-per-step", "1"]
 args = bench.parse_args()
 dev = torch.device("cuda", 0)
-sc, cams, dpix = bench.build_workload(args, 0, 1, dev)
+sc, cams, dpix, _all = bench.build_workload(args, 0, 1, dev)
 arm = bench.OursArm(args, sc, cams, dpix, dev)
 R, radii, st = arm.state_of_view(0)
 trav, contrib = st["pair_counts"]

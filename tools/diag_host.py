@@ -6,7 +6,7 @@ import torch, bench
 sys.argv = [sys.argv[0], "--gaussians", "2000", "--width", "64", "--height", "64"]
 args = bench.parse_args()
 dev = torch.device("cuda", 0)
-sc, cams, dpix = bench.build_workload(args, 0, 1, dev)
+sc, cams, dpix, _all = bench.build_workload(args, 0, 1, dev)
 arm = bench.OursArm(args, sc, cams, dpix, dev)
 for _ in range(5):
     arm.step()

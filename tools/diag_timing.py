@@ -5,7 +5,7 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "gaussian-splatting-slam_b200")]
 import torch, bench
 args = bench.parse_args()
 dev = torch.device("cuda", 0)
-sc, cams, dpix = bench.build_workload(args, 0, 1, dev)
+sc, cams, dpix, _all = bench.build_workload(args, 0, 1, dev)
 arm = bench.OursArm(args, sc, cams, dpix, dev)
 def stat(k): return torch.cuda.memory_stats().get(k, 0)
 for it in range(40):

@@ -7,7 +7,7 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 sys.argv = [sys.argv[0], "--views-per-step", "1"]
 args = bench.parse_args()
 dev = torch.device("cuda", 0)
-sc, cams, dpix = bench.build_workload(args, 0, 1, dev)
+sc, cams, dpix, _all = bench.build_workload(args, 0, 1, dev)
 arm = bench.OursArm(args, sc, cams, dpix, dev)
 for _ in range(n):
     arm.step()
