@@ -450,7 +450,7 @@ int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, doub
     return launch_adam(groups, n_groups, beta1, beta2, eps, visible, (cudaStream_t)stream);
 }
 
-size_t gsr_comm_signal_bytes(void) { return sizeof(uint32_t) * GSR_COMM_MAX_CTAS * GSR_COMM_MAX_PEERS; }
+size_t gsr_comm_signal_bytes(void) { return sizeof(uint32_t) * (GSR_COMM_MAX_CTAS * GSR_COMM_MAX_PEERS + 16); }   // + error word
 
 int gsr_comm_slice(long long numel, int rank, int world, long long* lo, long long* hi) {
     if (numel < 0 || (numel & 3) || world < 1 || world > GSR_COMM_MAX_PEERS || rank < 0 || rank >= world || !lo || !hi)
@@ -502,6 +502,34 @@ int gsr_exchange_adam_step(const gsr_peer_group* grads, const gsr_peer_group* pa
         return GSR_E_BADARG;
     return launch_exchange_adam(*grads, *params, exp_avg, exp_avg_sq, spans, n_spans, beta1, beta2, eps, numel, max_ctas,
                                 (cudaStream_t)stream);
+}
+
+size_t gsr_comm_emulation_scratch_bytes(void) { return comm_emulation_scratch_bytes(); }
+
+int gsr_allreduce_sum_emulated(const gsr_peer_group* groups, int world, long long numel, int max_ctas, void* scratch_dev,
+                               void* stream) {
+    if (!groups || !scratch_dev || world < 1 || world > GSR_COMM_MAX_PEERS || numel < 0 || (numel & 3) || max_ctas < 0) return GSR_E_BADARG;
+    if (numel == 0) return 0;
+    for (int r = 0; r < world; r++) {
+        if (groups[r].rank != r || groups[r].world != world || !peer_group_ok(groups[r], true)) return GSR_E_BADARG;
+    }
+    return launch_allreduce_sum_emulated(groups, world, numel, max_ctas, scratch_dev, (cudaStream_t)stream);
+}
+
+int gsr_exchange_adam_step_emulated(const gsr_peer_group* grads, const gsr_peer_group* params, float* const* exp_avg,
+                                    float* const* exp_avg_sq, int world, const gsr_adam_span* spans, int n_spans, double beta1,
+                                    double beta2, double eps, long long numel, int max_ctas, void* scratch_dev, void* stream) {
+    if (!grads || !params || !exp_avg || !exp_avg_sq || !scratch_dev || world < 1 || world > GSR_COMM_MAX_PEERS || numel < 0 ||
+        (numel & 3) || max_ctas < 0 || n_spans < 0 || n_spans > GSR_ADAM_MAX_SPANS || (n_spans > 0 && !spans))
+        return GSR_E_BADARG;
+    if (numel == 0) return 0;
+    for (int r = 0; r < world; r++) {
+        if (grads[r].rank != r || grads[r].world != world || !peer_group_ok(grads[r], true) || !peer_group_ok(params[r], false) ||
+            !exp_avg[r] || !exp_avg_sq[r])
+            return GSR_E_BADARG;
+    }
+    return launch_exchange_adam_emulated(grads, params, exp_avg, exp_avg_sq, world, spans, n_spans, beta1, beta2, eps, numel,
+                                         max_ctas, scratch_dev, (cudaStream_t)stream);
 }
 
 size_t gsr_densify_plan_bytes(int P) { return P < 0 ? 0 : densify_plan_bytes((size_t)P); }
@@ -560,6 +588,7 @@ int gsr_debug_blend_stats(const gsr_view* view, int R, const char* geom, const c
 }
 
 int gsr_debug_set_exact_cull(int on) { return set_exact_cull(on); }
+int gsr_debug_set_blend_variant(int v) { return set_blend_variant(v); }
 
 int gsr_debug_fp32_peak(int iters, float* out, int* sms_out, void* stream) {
     if (iters <= 0 || !out) return GSR_E_BADARG;

@@ -1,4 +1,4 @@
-// gsr_binning.cu -- depth ordering of Gaussians, tile-count scan + instance emission (one kernel), tile table
+// gsr_binning.cu -- depth ordering of Gaussians, tile-count scan, instance emission (balanced by output), tile table
 // (ranges + digit histograms), tile sort. Replaces rasterizer_impl.cu:70-138 (duplicateWithKeys, identifyTileRanges)
 // and the CUB calls at :277 (InclusiveSum) and :303 (SortPairs). HBM-bound integer work.
 //
@@ -8,10 +8,11 @@
 //                   are dropped by the sort's first pass, so 3 of the 4 passes, the scan and the emission run over
 //                   the visible count only -- half of P on the bench scene; that count stays on the device);
 //               (2) emit instances walking the Gaussians in that order (offsets from a scan taken in
-//                   the same order, inside the same kernel);  (3) stable sort of instances by tile id only.
+//                   the same order);  (3) stable sort of instances by tile id only.
 // The tile ranges (identifyTileRanges) and the digit histograms of (3) need no pass over the instances: every
 // rectangle adds +1 / -1 at its four corners of a difference array, whose 2-D prefix sum is the list length per tile.
 #include "gsr_common.cuh"
+#include <algorithm>
 
 namespace gsr {
 
@@ -51,49 +52,35 @@ __device__ __forceinline__ void rect_of(float px, float py, int max_radius, int 
     y1 = min(gy, max((int)0, (int)((py + max_radius + GSR_TILE - 1) / GSR_TILE)));
 }
 
-// One kernel replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:277) AND duplicateWithKeys (:70-111).
-//
-// Scan: single-pass chained scan (decoupled look-back) of the tile counts in DEPTH order. A CTA takes 1024 visible
-// Gaussians by ticket (which makes waiting on lower-numbered tiles safe whatever the CTA scheduling order), gathers
-// their packed rectangles through `order` (L2 hits: 4 B x P), scans locally, publishes its sum and looks back. A tile's
+// Replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:277): single-pass chained scan (decoupled look-back) of
+// the tile counts in DEPTH order. A CTA takes 1024 visible Gaussians by ticket (which makes waiting on lower-numbered
+// tiles safe whatever the CTA scheduling order), gathers their packed rectangles through `order` (L2 hits: 4 B x P),
+// scans locally, publishes its sum and looks back with ALL its threads (1024 predecessors per round trip). A tile's
 // status word carries flag (bits 30-31: 1 = the tile's own sum, 2 = inclusive prefix) and value (30 bits, saturating)
-// together, so one 32-bit store publishes both. status[0..m) = tile words, status[m_slots] = grand total,
-// status[m_slots + 1] = ticket; all zeroed before the launch.
-//
-// Emission: the CTA then writes the instances of its own Gaussians -- it knows their offsets, nothing goes through
-// memory in between. A warp takes 32 consecutive Gaussians; their output slots are one contiguous range, so the lanes
-// walk that range 32 slots at a time (coalesced stores). Owner of slot s = number of Gaussians whose range ends at or
-// before s; the ends are strictly increasing, so inside a window of 32 slots they are distinct bits: ONE warp-wide OR
-// (REDUX) of those bits plus a running count of the ends before the window gives the owner, four shuffles fetch its
-// id, range start, corner and width. Writes are clamped to `cap` (the blob's capacity): with a speculative capacity the
-// count may turn out larger, and then the caller repeats the binning.
-//
-// Tile table input: every Gaussian adds its rectangle to the difference array (4 RED operations).
+// together, so one 32-bit store publishes both. status[0..m) = tile words (all inclusive prefixes once the kernel has
+// finished: the emission uses them as the first level of its search), status[m_slots] = grand total,
+// status[m_slots + 1] = ticket; all zeroed before the launch. The rectangles are also written out in depth order.
 constexpr uint32_t kScanOwn = 1u << 30, kScanIncl = 2u << 30, kScanVal = (1u << 30) - 1u;
 template <bool PACKED>
-__global__ void __launch_bounds__(kScanThreads) scan_emit_kernel(const uint32_t* __restrict__ n_dev,
-                                                                  const uint32_t* __restrict__ order,
-                                                                  const uint32_t* __restrict__ counts,
-                                                                  const float4* __restrict__ rec,
-                                                                  const int* __restrict__ radii, int gx, int gy, int m_slots,
-                                                                  uint32_t* __restrict__ status,
-                                                                  uint32_t* __restrict__ point_offsets,
-                                                                  int32_t* __restrict__ tile_diff, uint32_t cap,
-                                                                  uint32_t* __restrict__ tile_keys,
-                                                                  uint32_t* __restrict__ vals) {
+__global__ void __launch_bounds__(kScanThreads) scan_offsets_kernel(const uint32_t* __restrict__ n_dev,
+                                                                     const uint32_t* __restrict__ order,
+                                                                     const uint32_t* __restrict__ counts, int m_slots,
+                                                                     uint32_t* __restrict__ status,
+                                                                     uint32_t* __restrict__ point_offsets,
+                                                                     uint32_t* __restrict__ rect_sorted) {
     // n (visible Gaussians, in depth order) lives on the device; the grid covers the host's upper bound and m_slots only
     // fixes where the total and the ticket sit. CTAs whose ticket lies beyond the last tile leave at once.
     __shared__ uint32_t warp_sums[kScanThreads / 32];
-    __shared__ uint32_t s_tile, s_prefix;
-    __shared__ uint32_t s_end[GSR_SCAN_TILE], s_gid[GSR_SCAN_TILE], s_xy[GSR_SCAN_TILE], s_bw[GSR_SCAN_TILE];
+    __shared__ uint32_t s_tile;
+    __shared__ unsigned long long s_part[kScanThreads / 32];
+    __shared__ int s_found[kScanThreads / 32];
     if (threadIdx.x == 0) s_tile = atomicAdd(status + m_slots + 1, 1u);
     __syncthreads();
     const int tile = (int)s_tile;
     const int n = (int)__ldg(n_dev);
     const int m = (n + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE;
     if (tile >= m) return;
-    const int tbase = tile * GSR_SCAN_TILE;
-    const int base = tbase + threadIdx.x * kScanItems;
+    const int base = tile * GSR_SCAN_TILE + threadIdx.x * kScanItems;
     uint32_t g[kScanItems] = {0u, 0u, 0u, 0u}, c[kScanItems], v = 0;
     if (base + kScanItems <= n) {
         const uint4 o4 = __ldg(reinterpret_cast<const uint4*>(order + base));     // base is a multiple of 4, order 128-byte aligned
@@ -103,128 +90,191 @@ __global__ void __launch_bounds__(kScanThreads) scan_emit_kernel(const uint32_t*
         for (int i = 0; i < kScanItems; i++)
             if (base + i < n) g[i] = __ldg(order + base + i);
     }
-    const int stride = gx + 1;
-#pragma unroll
-    for (int i = 0; i < kScanItems; i++) c[i] = (base + i < n) ? __ldg(counts + g[i]) : 0u;
-    int x0[kScanItems], y0[kScanItems], bw[kScanItems], bh[kScanItems];
 #pragma unroll
     for (int i = 0; i < kScanItems; i++) {
-        x0[i] = 0; y0[i] = 0; bw[i] = 1; bh[i] = 0;
+        c[i] = (base + i < n) ? __ldg(counts + g[i]) : 0u;
         if (PACKED) {
-            const uint32_t r = c[i];
-            x0[i] = (int)(r & 255u); y0[i] = (int)((r >> 8) & 255u); bw[i] = (int)((r >> 16) & 255u); bh[i] = (int)(r >> 24);
-            c[i] = (uint32_t)(bw[i] * bh[i]);
-        } else if (c[i] > 0u) {                         // grids above 255 x 255 tiles: rectangle from record + radius
-            int x1, y1;
-            const float4 r0 = __ldg(rec + 3 * (size_t)g[i]);
-            rect_of(r0.x, r0.y, __ldg(radii + g[i]), gx, gy, x0[i], y0[i], x1, y1);
-            bw[i] = x1 - x0[i]; bh[i] = y1 - y0[i];
+            if (base + i < n) rect_sorted[base + i] = c[i];
+            c[i] = ((c[i] >> 16) & 255u) * (c[i] >> 24);
         }
         v += c[i];
-        if (c[i] > 0u) {
-            // corners on the far border (x = gx or y = gy) are never read by the prefix sums: skipped
-            const int xe = x0[i] + bw[i], ye = y0[i] + bh[i];
-            atomicAdd(tile_diff + y0[i] * stride + x0[i], 1);
-            if (xe < gx) atomicAdd(tile_diff + y0[i] * stride + xe, -1);
-            if (ye < gy) atomicAdd(tile_diff + ye * stride + x0[i], -1);
-            if (xe < gx && ye < gy) atomicAdd(tile_diff + ye * stride + xe, 1);
-        }
     }
     uint32_t total;
     const uint32_t ex = block_exclusive_scan(v, warp_sums, total);
     volatile uint32_t* vs = status;
     if (threadIdx.x == 0) vs[tile] = (tile == 0 ? kScanIncl : kScanOwn) | total;
-    if (threadIdx.x < 32) {
-        // look-back, 128 predecessors per round trip: lane l reads tiles j - 4l .. j - 4l - 3 (nearest first).
-        const int lane = threadIdx.x;
-        // Saturating sums: a status word has 30 value bits, so a running prefix that reaches kScanVal = 2^30 - 1 stays
-        // there (sums are formed in 64 bits and clamped) instead of spilling into the flag bits. A total equal to
-        // kScanVal therefore means "num_rendered >= 2^30 - 1": gsr_forward answers GSR_E_TOOLARGE, and every consumer of
-        // the offsets clamps its writes to the capacity of the binning blob, so nothing is written out of bounds.
-        unsigned long long prefix = 0;
-        for (int j = tile - 1; j >= 0; j -= 128) {
-            unsigned long long part = 0;                   // sum of this lane's words up to (and including) its first inclusive one
-            bool has_incl = false;
+    // look-back with the whole CTA, 1024 predecessors per round trip: warp w reads tiles j - 128w - 4*lane - q (nearest
+    // first). Saturating sums: a status word has 30 value bits, so a running prefix that reaches kScanVal = 2^30 - 1 stays
+    // there (sums are formed in 64 bits and clamped) instead of spilling into the flag bits. A total equal to kScanVal
+    // therefore means "num_rendered >= 2^30 - 1": gsr_forward answers GSR_E_TOOLARGE, and every consumer of the offsets
+    // clamps its writes to the capacity of the binning blob, so nothing is written out of bounds.
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    unsigned long long prefix = 0;
+    for (int j = tile - 1; j >= 0; j -= 4 * kScanThreads) {
+        unsigned long long part = 0;                       // sum of this lane's words up to (and including) its first inclusive one
+        bool has_incl = false;
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const int idx = j - 4 * lane - q;
-                uint32_t st = kScanIncl;                   // before the first tile: inclusive prefix 0
-                if (idx >= 0) {
-                    st = vs[idx];
-                    while ((st >> 30) == 0u) { __nanosleep(20); st = vs[idx]; }
-                }
-                if (!has_incl) part += st & kScanVal;
-                has_incl = has_incl || (st >> 30) == 2u;
+        for (int q = 0; q < 4; q++) {
+            const int idx = j - 128 * w - 4 * lane - q;
+            uint32_t st = kScanIncl;                       // before the first tile: inclusive prefix 0
+            if (idx >= 0) {
+                st = vs[idx];
+                while ((st >> 30) == 0u) { __nanosleep(20); st = vs[idx]; }
             }
-            const unsigned incl = __ballot_sync(0xffffffffu, has_incl);
-            const int first = incl ? __ffs(incl) - 1 : 31;
-            unsigned long long val = lane <= first ? part : 0ull;      // <= 4 * 2^30 per lane, 2^37 per warp
+            if (!has_incl) part += st & kScanVal;
+            has_incl = has_incl || (st >> 30) == 2u;
+        }
+        const unsigned incl = __ballot_sync(0xffffffffu, has_incl);
+        const int first = incl ? __ffs(incl) - 1 : 31;
+        unsigned long long val = lane <= first ? part : 0ull;          // <= 4 * 2^30 per lane, 2^37 per warp
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
-            prefix += val;
-            if (incl) break;
+        for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+        if (lane == 0) { s_part[w] = val; s_found[w] = incl != 0u; }
+        __syncthreads();
+        bool done = false;
+#pragma unroll
+        for (int k = 0; k < kScanThreads / 32; k++) {
+            if (!done) prefix += s_part[k];
+            done = done || s_found[k] != 0;
         }
-        if (lane == 0) {
-            const unsigned long long incl_sum = prefix + total;
-            const uint32_t sat = incl_sum >= kScanVal ? kScanVal : (uint32_t)incl_sum;
-            if (tile > 0) vs[tile] = kScanIncl | sat;
-            if (tile == m - 1) status[m_slots] = sat;
-            s_prefix = prefix >= kScanVal ? kScanVal : (uint32_t)prefix;
-        }
+        __syncthreads();
+        if (done) break;
     }
-    __syncthreads();
-    const uint32_t tile_start = s_prefix;
-    uint32_t run = ex + tile_start;
+    if (threadIdx.x == 0) {
+        const unsigned long long incl_sum = prefix + total;
+        const uint32_t sat = incl_sum >= kScanVal ? kScanVal : (uint32_t)incl_sum;
+        if (tile > 0) vs[tile] = kScanIncl | sat;
+        if (tile == m - 1) status[m_slots] = sat;
+    }
+    uint32_t run = ex + (prefix >= kScanVal ? kScanVal : (uint32_t)prefix);
 #pragma unroll
     for (int i = 0; i < kScanItems; i++) {
         run += c[i];
-        const int k = threadIdx.x * kScanItems + i;
-        s_end[k] = run;
-        s_gid[k] = g[i];
-        s_xy[k] = (uint32_t)x0[i] | ((uint32_t)y0[i] << 16);
-        s_bw[k] = (uint32_t)max(1, bw[i]);
         if (base + i < n) point_offsets[base + i] = run;   // inclusive, as rasterizer_impl.cu:277 (in depth order)
     }
+}
+
+// Replaces duplicateWithKeys (rasterizer_impl.cu:70-111), balanced by OUTPUT: a CTA writes 4096 consecutive instance
+// slots, whatever number of Gaussians they belong to. (Emitting per Gaussian -- the reference's mapping, one thread per
+// Gaussian -- leaves the near Gaussians, which cover hundreds of tiles each and come first in depth order, to a few
+// threads while the rest of the GPU idles.) The CTA finds the Gaussians that own its slots in two cooperative steps,
+// both counts over sorted arrays: the scan's per-1024 inclusive prefixes give the first and last scan tile, the offsets
+// of those two tiles the first and last Gaussian. Their offsets / ids / rectangles (<= 4097 of each) are staged in shared
+// memory; a slot's owner is the number of range ends at or before it: the ends are strictly increasing, so they are
+// distinct bits of a 4096-bit map, and the owner is a prefix popcount. Stores are coalesced, writes clamped to `cap`.
+constexpr int kEmitThreads = 256;
+constexpr int kEmitTile = GSR_SORT_TILE;                    // 4096 slots per CTA = one tile of the instance sort
+constexpr int kEmitMax = kEmitTile + 8;                     // Gaussians a CTA can need (4097), padded
+template <bool PACKED>
+__global__ void __launch_bounds__(kEmitThreads) emit_instances_kernel(const uint32_t* __restrict__ n_dev,
+                                                                       const uint32_t* __restrict__ status, int m_slots,
+                                                                       const uint32_t* __restrict__ offsets,
+                                                                       const uint32_t* __restrict__ order,
+                                                                       const uint32_t* __restrict__ rect_sorted,
+                                                                       const float4* __restrict__ rec,
+                                                                       const int* __restrict__ radii, int gx, int gy,
+                                                                       uint32_t cap, uint32_t* __restrict__ tile_keys,
+                                                                       uint32_t* __restrict__ vals) {
+    extern __shared__ __align__(16) uint32_t emit_smem[];
+    uint32_t* s_end = emit_smem;                            // [kEmitMax] inclusive end offset of the k-th Gaussian of the CTA
+    uint32_t* s_gid = s_end + kEmitMax;
+    uint32_t* s_rect = s_gid + kEmitMax;                    // PACKED: x0 | y0 << 8 | w << 16 | h << 24;  else x0 | y0 << 16
+    uint32_t* s_bw = s_rect + kEmitMax;                     // !PACKED only: rectangle width
+    __shared__ uint32_t s_bits[kEmitTile / 32];             // bit r of the map: some Gaussian's range ends at slot base + r
+    __shared__ uint32_t s_wpre[kEmitTile / 32];             // ends in the words before this one
+    __shared__ int s_cnt[4];
+    const int t = threadIdx.x;
+    const uint32_t total = min(__ldg(status + m_slots), cap);
+    const uint32_t base = blockIdx.x * (uint32_t)kEmitTile;
+    if (base >= total) return;
+    const uint32_t stop = min(base + (uint32_t)kEmitTile, total);        // slots [base, stop)
+    const int n = (int)__ldg(n_dev);
+    const int m = (n + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE;
+    if (t < 4) s_cnt[t] = 0;
+    for (int i = t; i < kEmitTile / 32; i += kEmitThreads) s_bits[i] = 0u;
     __syncthreads();
-    if (tile_start >= cap) return;                         // everything this tile would write lies beyond the capacity
-    // ---- emission: warp w takes Gaussians w*128 + r*32 + lane of the tile
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-#pragma unroll 1
-    for (int r = 0; r < GSR_SCAN_TILE / kScanThreads; r++) {
-        const int k = w * (GSR_SCAN_TILE / 8) + r * 32 + lane;
-        const int j = tbase + k;
-        if (j - lane >= n) break;
-        uint32_t gid = 0, end = 0, start = 0, xy = 0;
-        int obw_mine = 1;
-        if (j < n) {
-            gid = s_gid[k]; end = s_end[k]; xy = s_xy[k]; obw_mine = (int)s_bw[k];
-            start = k > 0 ? s_end[k - 1] : tile_start;
+    // level 1: scan tiles. t_lo = tiles whose inclusive prefix is <= base (they end before our first slot);
+    //          t_hi = tiles whose inclusive prefix is < stop (the tile after them holds the Gaussian that owns slot stop-1)
+    {
+        int lo = 0, hi = 0;
+        for (int i = t; i < m; i += kEmitThreads) {
+            const uint32_t incl = __ldg(status + i) & kScanVal;
+            lo += incl <= base;
+            hi += incl < stop;
         }
-        // lanes beyond n: end = start = end of the last valid lane, so they never own a slot that is written
-        const uint32_t last_end = __shfl_sync(0xffffffffu, end, min(31, n - 1 - (j - lane)));
-        if (j >= n) { end = last_end; start = last_end; }
-        const uint32_t first = __shfl_sync(0xffffffffu, start, 0);
-        const uint32_t stop = min(last_end, cap);
-        uint32_t before = 0;                            // ends below the window's first slot (warp-uniform)
-        for (uint32_t wb = first; wb < stop; wb += 32) {
-            const uint32_t rel = end - wb;              // wraps to a huge value for ends below the window
-            const uint32_t mine = (rel < 32u && j < n) ? (1u << rel) : 0u;
-            const uint32_t ends = __reduce_or_sync(0xffffffffu, mine);
-            const uint32_t s = wb + lane;
-            const int owner = min((int)(before + __popc(ends & (0xffffffffu >> (31 - lane)))), 31);
-            before += __popc(ends);
-            const uint32_t og = __shfl_sync(0xffffffffu, gid, owner);
-            const uint32_t ostart = __shfl_sync(0xffffffffu, start, owner);
-            const uint32_t oxy = __shfl_sync(0xffffffffu, xy, owner);
-            const int obw = __shfl_sync(0xffffffffu, obw_mine, owner);
-            if (s < stop) {
-                const uint32_t q = s - ostart;                             // row-major index inside the rectangle
-                const int row = (int)(((float)q + 0.5f) * __frcp_rn((float)obw));   // exact: the quotient stays >= 0.5 / 4096 away
-                const int col = (int)q - row * obw;                        //        from an integer, the product errs by < 1e-3 of that
-                tile_keys[s] = (uint32_t)(((int)(oxy >> 16) + row) * gx + (int)(oxy & 0xffffu) + col);
-                vals[s] = og;
-            }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { lo += __shfl_xor_sync(0xffffffffu, lo, o); hi += __shfl_xor_sync(0xffffffffu, hi, o); }
+        if ((t & 31) == 0) { atomicAdd(&s_cnt[0], lo); atomicAdd(&s_cnt[1], hi); }
+    }
+    __syncthreads();
+    const int t_lo = s_cnt[0], t_hi = min(s_cnt[1], m - 1);
+    // level 2: Gaussians inside those two tiles. j_lo = first Gaussian whose end is > base; j_hi = first whose end is >= stop
+    {
+        int lo = 0, hi = 0;
+        for (int i = t; i < GSR_SCAN_TILE; i += kEmitThreads) {
+            const int ja = t_lo * GSR_SCAN_TILE + i, jb = t_hi * GSR_SCAN_TILE + i;
+            if (ja < n) lo += __ldg(offsets + ja) <= base;
+            if (jb < n) hi += __ldg(offsets + jb) < stop;
         }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { lo += __shfl_xor_sync(0xffffffffu, lo, o); hi += __shfl_xor_sync(0xffffffffu, hi, o); }
+        if ((t & 31) == 0) { atomicAdd(&s_cnt[2], lo); atomicAdd(&s_cnt[3], hi); }
+    }
+    __syncthreads();
+    const int j_lo = t_lo * GSR_SCAN_TILE + s_cnt[2];
+    const int j_hi = min(t_hi * GSR_SCAN_TILE + s_cnt[3], n - 1);
+    const int cnt = min(j_hi - j_lo + 1, kEmitMax - 1);    // 1 .. 4097 (ends are strictly increasing: every visible Gaussian has >= 1 tile)
+    const uint32_t first_start = j_lo > 0 ? __ldg(offsets + j_lo - 1) : 0u;
+    for (int k = t; k < cnt; k += kEmitThreads) {
+        const int j = j_lo + k;
+        const uint32_t e = __ldg(offsets + j), gid = __ldg(order + j);
+        s_end[k] = e;
+        s_gid[k] = gid;
+        if (PACKED) {
+            s_rect[k] = __ldg(rect_sorted + j);
+        } else {                                            // grids above 255 x 255 tiles: rectangle from record + radius
+            int x0, y0, x1, y1;
+            const float4 r0 = __ldg(rec + 2 * (size_t)gid);
+            rect_of(r0.x, r0.y, __ldg(radii + gid), gx, gy, x0, y0, x1, y1);
+            s_rect[k] = (uint32_t)x0 | ((uint32_t)y0 << 16);
+            s_bw[k] = (uint32_t)max(1, x1 - x0);
+        }
+        const uint32_t rel = e - base;                      // e > base for every k (j >= j_lo)
+        if (rel < (uint32_t)kEmitTile) atomicOr(&s_bits[rel >> 5], 1u << (rel & 31u));
+    }
+    __syncthreads();
+    if (t < 32) {                                           // exclusive prefix of the words' popcounts (128 words: 4 per lane)
+        uint32_t c4[4], sum = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) { c4[q] = __popc(s_bits[4 * t + q]); sum += c4[q]; }
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (t >= o) incl += y;
+        }
+        uint32_t run = incl - sum;
+#pragma unroll
+        for (int q = 0; q < 4; q++) { s_wpre[4 * t + q] = run; run += c4[q]; }
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int i = 0; i < kEmitTile / kEmitThreads; i++) {
+        const uint32_t r = (uint32_t)(i * kEmitThreads + t);           // slot base + r
+        if (base + r >= stop) break;
+        // owner = Gaussians of the CTA's list whose range ends at or before this slot, i.e. end - base <= r
+        const uint32_t wd = r >> 5, bit = r & 31u;
+        const int k = (int)(s_wpre[wd] + __popc(s_bits[wd] & (0xffffffffu >> (31u - bit))));
+        const uint32_t start = k > 0 ? s_end[k - 1] : first_start;
+        const uint32_t q = base + r - start;                            // row-major index inside the rectangle
+        const uint32_t rc = s_rect[k];
+        int x0, y0, bw;
+        if (PACKED) { x0 = (int)(rc & 255u); y0 = (int)((rc >> 8) & 255u); bw = max(1, (int)((rc >> 16) & 255u)); }
+        else { x0 = (int)(rc & 0xffffu); y0 = (int)(rc >> 16); bw = (int)s_bw[k]; }
+        const int row = (int)(((float)q + 0.5f) * __frcp_rn((float)bw));   // exact: the quotient stays >= 0.5 / 4096 away
+        const int col = (int)q - row * bw;                                  //        from an integer, the product errs by < 1e-3 of that
+        tile_keys[base + r] = (uint32_t)((y0 + row) * gx + x0 + col);
+        vals[base + r] = s_gid[k];
     }
 }
 
@@ -269,63 +319,159 @@ int launch_depth_order(const gsr_view& v, GeomState& g, cudaStream_t s) {
 }
 
 // ------------------------------------------------------------------ tile table (A9 + the histograms of A8)
-// One CTA. The difference array's 2-D prefix sum is the number of instances per tile; their exclusive scan in tile order
-// gives the ranges (identifyTileRanges, rasterizer_impl.cu:116-138: empty tiles keep (0, 0), :310), and the counts binned
-// by the digits of the tile id are the histograms the instance sort's passes start from -- no pass over the instances.
+// Every visible Gaussian adds +1 / -1 at the four corners of its tile rectangle to a difference array; the array's 2-D
+// prefix sum is the number of instances per tile. Their exclusive scan in tile order gives the ranges (identifyTileRanges,
+// rasterizer_impl.cu:116-138: empty tiles keep (0, 0), :310), and the counts binned by the digits of the tile id are the
+// histograms the instance sort's passes start from -- no pass over the instances for either.
+//
+// Straight global REDs for the corners are out: they pile up on the cells around the image centre, and same-address
+// reductions serialise in L2 at ~30 ns each (measured: 5.9M REDs on 8349 cells cost 0.15 ms). So a few persistent CTAs
+// accumulate their share of the Gaussians in shared memory (the rectangles stream in coalesced, 16 bytes per thread, in id
+// order -- no depth order needed) and flush their non-zero cells with one RED each; the LAST CTA to finish (a counter in
+// global memory) then turns the array into ranges and histograms, so the table costs one launch.
 constexpr int kTableThreads = 1024;
 constexpr int kTableSmemMax = 200 * 1024;
-__global__ void __launch_bounds__(kTableThreads) tile_table_kernel(int32_t* __restrict__ diff, int gx, int gy, int passes,
-                                                                    int total_bits, uint2* __restrict__ ranges,
-                                                                    uint32_t* __restrict__ ghist, int use_smem) {
-    extern __shared__ __align__(16) int32_t table_smem[];
-    __shared__ uint32_t hist[4][GSR_RADIX];
-    __shared__ uint32_t warp_sums[kTableThreads / 32];
-    const int t = threadIdx.x, stride = gx + 1, cells = stride * (gy + 1);
-    int32_t* work = use_smem ? table_smem : diff;          // large grids: in place in global memory (slow path, correct)
-    if (use_smem)
-        for (int i = t; i < cells; i += kTableThreads) work[i] = diff[i];
+
+__device__ __forceinline__ void diff_add_rect(int32_t* acc, int stride, int gx, int gy, int x0, int y0, int bw, int bh) {
+    // corners on the far border (x = gx or y = gy) are never read by the prefix sums: skipped
+    const int xe = x0 + bw, ye = y0 + bh;
+    atomicAdd(acc + y0 * stride + x0, 1);
+    if (xe < gx) atomicAdd(acc + y0 * stride + xe, -1);
+    if (ye < gy) atomicAdd(acc + ye * stride + x0, -1);
+    if (xe < gx && ye < gy) atomicAdd(acc + ye * stride + xe, 1);
+}
+
+// the table itself, run by one CTA of kTableThreads threads. `work` holds the difference array (shared memory copy, or
+// the global array itself for grids too large for shared memory: slow path, correct).
+__device__ void tile_table_block(int32_t* work, int gx, int gy, int passes, int total_bits, uint2* __restrict__ ranges,
+                                 uint32_t* __restrict__ ghist, uint32_t (*hist)[GSR_RADIX], uint32_t* warp_sums) {
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5, stride = gx + 1;
     for (int i = t; i < 4 * GSR_RADIX; i += kTableThreads) (&hist[0][0])[i] = 0u;
-    __syncthreads();
-    for (int x = t; x < gx; x += kTableThreads) {          // prefix down every column
-        int32_t run = 0;
-        for (int y = 0; y < gy; y++) { run += work[y * stride + x]; work[y * stride + x] = run; }
+    // prefix along every row, one warp per row, 32 columns per step with a carried sum
+    for (int y = w; y < gy; y += kTableThreads / 32) {
+        int32_t carry = 0;
+        for (int x0 = 0; x0 < gx; x0 += 32) {
+            const int x = x0 + lane;
+            int32_t v = x < gx ? work[y * stride + x] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int32_t u = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += u;
+            }
+            v += carry;
+            if (x < gx) work[y * stride + x] = v;
+            carry = __shfl_sync(0xffffffffu, v, 31);
+        }
     }
     __syncthreads();
-    for (int y = t; y < gy; y += kTableThreads) {          // prefix along every row: work[y][x] = instances of tile (x, y)
+    for (int x = t; x < gx; x += kTableThreads) {          // prefix down every column: work[y][x] = instances of tile (x, y)
         int32_t run = 0;
-        for (int x = 0; x < gx; x++) { run += work[y * stride + x]; work[y * stride + x] = run; }
+        for (int y = 0; y < gy; y++) { run += work[y * stride + x]; work[y * stride + x] = run; }
     }
     __syncthreads();
     const int tiles = gx * gy;
     const int per = (tiles + kTableThreads - 1) / kTableThreads;
     const int lo = min(t * per, tiles), hi = min(lo + per, tiles);
     uint32_t local = 0;
-    for (int k = lo; k < hi; k++) local += (uint32_t)work[(k / gx) * stride + (k % gx)];
-    // exclusive scan of `local` over the 1024 threads
-    const int lane = t & 31, w = t >> 5;
-    uint32_t incl = local;
+    {
+        int y = lo / gx, x = lo - y * gx;
+        for (int k = lo; k < hi; k++) {
+            local += (uint32_t)work[y * stride + x];
+            if (++x == gx) { x = 0; y++; }
+        }
+    }
+    uint32_t incl = local;                                  // exclusive scan of `local` over the 1024 threads
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += y;
+        const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += u;
     }
     if (lane == 31) warp_sums[w] = incl;
     __syncthreads();
     uint32_t ofs = incl - local;
     for (int k = 0; k < w; k++) ofs += warp_sums[k];
-    for (int k = lo; k < hi; k++) {
-        const uint32_t c = (uint32_t)work[(k / gx) * stride + (k % gx)];
-        ranges[k] = c ? make_uint2(ofs, ofs + c) : make_uint2(0u, 0u);
-        ofs += c;
-        if (c) {
-            for (int p = 0; p < passes; p++) {
-                const int bits = min(8, total_bits - 8 * p);
-                atomicAdd(&hist[p][((uint32_t)k >> (8 * p)) & ((1u << bits) - 1u)], c);
+    {
+        int y = lo / gx, x = lo - y * gx;
+        for (int k = lo; k < hi; k++) {
+            const uint32_t c = (uint32_t)work[y * stride + x];
+            ranges[k] = c ? make_uint2(ofs, ofs + c) : make_uint2(0u, 0u);
+            ofs += c;
+            if (c) {
+                for (int p = 0; p < passes; p++) {
+                    const int bits = min(8, total_bits - 8 * p);
+                    atomicAdd(&hist[p][((uint32_t)k >> (8 * p)) & ((1u << bits) - 1u)], c);
+                }
             }
+            if (++x == gx) { x = 0; y++; }
         }
     }
     __syncthreads();
     for (int i = t; i < passes * GSR_RADIX; i += kTableThreads) ghist[i] = (&hist[0][0])[i];
+}
+
+template <bool PACKED>
+__global__ void __launch_bounds__(kTableThreads) tile_table_kernel(int P, const uint32_t* __restrict__ counts,
+                                                                    const float4* __restrict__ rec,
+                                                                    const int* __restrict__ radii, int gx, int gy,
+                                                                    int32_t* __restrict__ tile_diff, int use_smem,
+                                                                    uint32_t* __restrict__ done_counter, int passes,
+                                                                    int total_bits, uint2* __restrict__ ranges,
+                                                                    uint32_t* __restrict__ ghist) {
+    extern __shared__ __align__(16) int32_t table_smem[];
+    __shared__ uint32_t hist[4][GSR_RADIX];
+    __shared__ uint32_t warp_sums[kTableThreads / 32];
+    __shared__ int s_last;
+    const int t = threadIdx.x, stride = gx + 1, cells = stride * (gy + 1);
+    int32_t* acc = use_smem ? table_smem : tile_diff;
+    if (use_smem) {
+        for (int i = t; i < cells; i += kTableThreads) acc[i] = 0;
+        __syncthreads();
+    }
+    // this CTA's share of the Gaussians: four per thread and step (16-byte loads; `counts` is 128-byte aligned)
+    const int nvec = P >> 2;
+    const uint4* c4 = reinterpret_cast<const uint4*>(counts);
+    for (int i = blockIdx.x * kTableThreads + t; i < nvec + 1; i += gridDim.x * kTableThreads) {
+        uint32_t c[4] = {0u, 0u, 0u, 0u};
+        if (i < nvec) { const uint4 v = __ldg(c4 + i); c[0] = v.x; c[1] = v.y; c[2] = v.z; c[3] = v.w; }
+        else { for (int q = 0; q < (P & 3); q++) c[q] = __ldg(counts + 4 * nvec + q); }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if (c[q] == 0u) continue;                               // culled
+            int x0, y0, bw, bh;
+            if (PACKED) {
+                x0 = (int)(c[q] & 255u); y0 = (int)((c[q] >> 8) & 255u); bw = (int)((c[q] >> 16) & 255u); bh = (int)(c[q] >> 24);
+            } else {
+                const int g = 4 * i + q;
+                int x1, y1;
+                const float4 r0 = __ldg(rec + 2 * (size_t)g);
+                rect_of(r0.x, r0.y, __ldg(radii + g), gx, gy, x0, y0, x1, y1);
+                bw = x1 - x0; bh = y1 - y0;
+            }
+            diff_add_rect(acc, stride, gx, gy, x0, y0, bw, bh);
+        }
+    }
+    if (use_smem) {
+        __syncthreads();
+        if (gridDim.x > 1) {
+            for (int i = t; i < cells; i += kTableThreads) {
+                const int32_t v = acc[i];
+                if (v != 0) atomicAdd(tile_diff + i, v);
+            }
+        }
+    }
+    if (gridDim.x > 1) {
+        // the last CTA to arrive builds the table from the complete array
+        __threadfence();
+        __syncthreads();
+        if (t == 0) s_last = atomicAdd(done_counter, 1u) == gridDim.x - 1 ? 1 : 0;
+        __syncthreads();
+        if (!s_last) return;
+        __threadfence();
+        if (use_smem)
+            for (int i = t; i < cells; i += kTableThreads) acc[i] = __ldcg(tile_diff + i);
+    }
+    __syncthreads();
+    tile_table_block(acc, gx, gy, passes, total_bits, ranges, ghist, hist, warp_sums);
 }
 
 static int bits_for(uint32_t count) {   // bits needed to represent ids 0..count-1
@@ -347,23 +493,53 @@ int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningSta
     // make the sorted result land in point_list
     uint32_t *ka = b.tile_keys, *va = b.point_list, *kb = b.tile_keys_tmp, *vb = b.vals_tmp;
     if (passes % 2) { ka = b.tile_keys_tmp; va = b.vals_tmp; kb = b.tile_keys; vb = b.point_list; }
-    if (cap > 0) {
-        if (rect_packing_ok(v.W, v.H))
-            GSR_LAUNCH("scan_emit", v.debug, s,
-                       (scan_emit_kernel<true><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.rect_packed, g.rec, radii, gx, gy, m,
-                                                                         b.scan_sums, g.point_offsets, b.tile_diff, cap, ka, va)));
-        else
-            GSR_LAUNCH("scan_emit", v.debug, s,
-                       (scan_emit_kernel<false><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.tiles_touched, g.rec, radii, gx, gy, m,
-                                                                          b.scan_sums, g.point_offsets, b.tile_diff, cap, ka, va)));
+    // tile table first: it streams the packed rectangles (12 MB at 3M Gaussians), which leaves them in L2 for the scan's
+    // gather through `order`
+    {
+        const size_t table_bytes = BinningState::diff_cells(v.W, v.H) * sizeof(int32_t);
+        const int use_smem = table_bytes <= (size_t)kTableSmemMax ? 1 : 0;
+        int sms = 148;
+        { const int e = sm_count(&sms); if (e) return e; }
+        // one CTA per ~32K Gaussians, at most one per SM: a single CTA (small scenes) needs no flush and no hand-over
+        const int blocks = std::max(1, std::min((v.P + 32767) / 32768, sms));
+        const size_t dyn = use_smem ? table_bytes : 0;
+        uint32_t* done_counter = b.scan_sums + m + 2;           // zeroed with the scan words
+        static DeviceOnce once_p, once_u;
+        if (rect_packing_ok(v.W, v.H)) {
+            { const int e = ensure_dynamic_smem(tile_table_kernel<true>, kTableSmemMax, once_p); if (e) return e; }
+            GSR_LAUNCH("tile_table", v.debug, s, (tile_table_kernel<true><<<blocks, kTableThreads, dyn, s>>>(
+                           v.P, g.rect_packed, g.rec, radii, gx, gy, b.tile_diff, use_smem, done_counter, passes, tbits, img.ranges,
+                           b.sort_scratch)));
+        } else {
+            { const int e = ensure_dynamic_smem(tile_table_kernel<false>, kTableSmemMax, once_u); if (e) return e; }
+            GSR_LAUNCH("tile_table", v.debug, s, (tile_table_kernel<false><<<blocks, kTableThreads, dyn, s>>>(
+                           v.P, g.tiles_touched, g.rec, radii, gx, gy, b.tile_diff, use_smem, done_counter, passes, tbits, img.ranges,
+                           b.sort_scratch)));
+        }
     }
-    const size_t table_bytes = BinningState::diff_cells(v.W, v.H) * sizeof(int32_t);
-    const int use_smem = table_bytes <= (size_t)kTableSmemMax ? 1 : 0;
-    static DeviceOnce once;
-    { const int e = ensure_dynamic_smem(tile_table_kernel, kTableSmemMax, once); if (e) return e; }
-    GSR_LAUNCH("tile_table", v.debug, s,
-               (tile_table_kernel<<<1, kTableThreads, use_smem ? table_bytes : 0, s>>>(b.tile_diff, gx, gy, passes, tbits, img.ranges,
-                                                                                     b.sort_scratch, use_smem)));
+    if (cap > 0) {
+        const int emit_blocks = (int)((cap + (uint32_t)kEmitTile - 1) / (uint32_t)kEmitTile);
+        static DeviceOnce once_ep, once_eu;
+        if (rect_packing_ok(v.W, v.H)) {
+            const size_t smem = sizeof(uint32_t) * 3 * kEmitMax;
+            { const int e = ensure_dynamic_smem(emit_instances_kernel<true>, (int)smem, once_ep); if (e) return e; }
+            GSR_LAUNCH("scan_offsets", v.debug, s,
+                       (scan_offsets_kernel<true><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.rect_packed, m, b.scan_sums,
+                                                                            g.point_offsets, g.rect_sorted)));
+            GSR_LAUNCH("emit_instances", v.debug, s,
+                       (emit_instances_kernel<true><<<emit_blocks, kEmitThreads, smem, s>>>(
+                           g.n_visible, b.scan_sums, m, g.point_offsets, g.order, g.rect_sorted, g.rec, radii, gx, gy, cap, ka, va)));
+        } else {
+            const size_t smem = sizeof(uint32_t) * 4 * kEmitMax;
+            { const int e = ensure_dynamic_smem(emit_instances_kernel<false>, (int)smem, once_eu); if (e) return e; }
+            GSR_LAUNCH("scan_offsets", v.debug, s,
+                       (scan_offsets_kernel<false><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.tiles_touched, m, b.scan_sums,
+                                                                             g.point_offsets, nullptr)));
+            GSR_LAUNCH("emit_instances", v.debug, s,
+                       (emit_instances_kernel<false><<<emit_blocks, kEmitThreads, smem, s>>>(
+                           g.n_visible, b.scan_sums, m, g.point_offsets, g.order, nullptr, g.rec, radii, gx, gy, cap, ka, va)));
+        }
+    }
     if (cap == 0) return 0;
     bool in_a = true;
     const SortOptions opt{/*hist_ready=*/true, /*n_dev=*/*total_dev, /*values_only_last=*/true};

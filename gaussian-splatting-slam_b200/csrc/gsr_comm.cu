@@ -32,24 +32,43 @@ struct CommArgs {
     long long lo, hi;                   // this rank's slice in 16-byte units
 };
 
-// signal pad protocol: slot (cta, source rank) on the destination's pad goes 0 -> 1 by the source, 1 -> 0 by the owner
-__device__ __forceinline__ void sig_put(uint32_t* slot) {
-    cuda::atomic_ref<uint32_t, cuda::thread_scope_system> ref(*slot);
-    uint32_t expect = 0;
-    while (!ref.compare_exchange_strong(expect, 1u, cuda::std::memory_order_release, cuda::std::memory_order_relaxed)) expect = 0;
+// signal pad protocol: slot (cta, source rank) on the destination's pad goes 0 -> 1 by the source, 1 -> 0 by the owner.
+// The spins are BOUNDED: a peer that never arrives (crashed process, a rank whose grid is not fully resident) would
+// otherwise hang every rank for ever. After ~2^26 polls with back-off (tens of seconds) the CTA sets the error word of
+// its own pad (slot GSR_COMM_MAX_CTAS * GSR_COMM_MAX_PEERS) and traps; the host sees the launch failure on its next
+// synchronisation instead of a silent hang.
+constexpr uint32_t kSpinLimit = 1u << 26;
+__device__ __forceinline__ void sig_fail(uint32_t* pad) {
+    atomicExch(pad + (size_t)GSR_COMM_MAX_CTAS * GSR_COMM_MAX_PEERS, 1u);
+    __threadfence_system();
+    __trap();
 }
-__device__ __forceinline__ void sig_wait(uint32_t* slot) {
+__device__ __forceinline__ void sig_put(uint32_t* slot, uint32_t* my_pad) {
     cuda::atomic_ref<uint32_t, cuda::thread_scope_system> ref(*slot);
-    uint32_t expect = 1;
-    while (!ref.compare_exchange_strong(expect, 0u, cuda::std::memory_order_acquire, cuda::std::memory_order_relaxed)) expect = 1;
+    uint32_t expect = 0, spins = 0;
+    while (!ref.compare_exchange_strong(expect, 1u, cuda::std::memory_order_release, cuda::std::memory_order_relaxed)) {
+        expect = 0;
+        if (++spins > 1024u) __nanosleep(256);
+        if (spins > kSpinLimit) sig_fail(my_pad);
+    }
 }
-__device__ __forceinline__ void twin_barrier(const CommArgs& a) {
+__device__ __forceinline__ void sig_wait(uint32_t* slot, uint32_t* my_pad) {
+    cuda::atomic_ref<uint32_t, cuda::thread_scope_system> ref(*slot);
+    uint32_t expect = 1, spins = 0;
+    while (!ref.compare_exchange_strong(expect, 0u, cuda::std::memory_order_acquire, cuda::std::memory_order_relaxed)) {
+        expect = 1;
+        if (++spins > 1024u) __nanosleep(256);
+        if (spins > kSpinLimit) sig_fail(my_pad);
+    }
+}
+// cta = index of this CTA among the rank's CTAs (blockIdx.x of a real launch)
+__device__ __forceinline__ void twin_barrier(const CommArgs& a, int cta) {
     __threadfence_system();
     __syncthreads();
     if ((int)threadIdx.x < a.world) {
         const int peer = threadIdx.x;
-        sig_put(a.sig[peer] + (size_t)blockIdx.x * GSR_COMM_MAX_PEERS + a.rank);
-        sig_wait(a.sig[a.rank] + (size_t)blockIdx.x * GSR_COMM_MAX_PEERS + peer);
+        sig_put(a.sig[peer] + (size_t)cta * GSR_COMM_MAX_PEERS + a.rank, a.sig[a.rank]);
+        sig_wait(a.sig[a.rank] + (size_t)cta * GSR_COMM_MAX_PEERS + peer, a.sig[a.rank]);
     }
     __syncthreads();
 }
@@ -76,12 +95,12 @@ __device__ __forceinline__ void peer_st(float4* p, float4 v) {
 }
 
 template <bool MULTICAST, int WORLD>
-__global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_kernel(const __grid_constant__ CommArgs a) {
-    twin_barrier(a);
-    const long long stride = (long long)gridDim.x * kCommThreads;
+__device__ __forceinline__ void allreduce_sum_body(const CommArgs& a, int cta, int n_ctas) {
+    twin_barrier(a, cta);
+    const long long stride = (long long)n_ctas * kCommThreads;
     const int world = WORLD > 0 ? WORLD : a.world;
     constexpr int U = MULTICAST ? kCommUnrollMc : kCommUnroll;
-    for (long long i0 = a.lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < a.hi; i0 += stride * U) {
+    for (long long i0 = a.lo + (long long)cta * kCommThreads + threadIdx.x; i0 < a.hi; i0 += stride * U) {
         float4 v[U];
         if (MULTICAST) {
 #pragma unroll
@@ -118,7 +137,17 @@ __global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_kernel(const __
             }
         }
     }
-    twin_barrier(a);
+    twin_barrier(a, cta);
+}
+
+template <bool MULTICAST, int WORLD>
+__global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_kernel(const __grid_constant__ CommArgs a) {
+    allreduce_sum_body<MULTICAST, WORLD>(a, (int)blockIdx.x, (int)gridDim.x);
+}
+// Emulated ranks on ONE device (tests without a second GPU): a single cooperative launch whose blockIdx.y is the rank.
+// Separate launches that wait for one another are not guaranteed to run at the same time; one cooperative grid is.
+__global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_emulated_kernel(const CommArgs* __restrict__ all) {
+    allreduce_sum_body<false, 0>(all[blockIdx.y], (int)blockIdx.x, (int)gridDim.x);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -138,12 +167,12 @@ struct ExchangeAdamArgs {
 };
 
 template <bool MULTICAST, int WORLD>
-__global__ void __launch_bounds__(kCommThreads, 2) exchange_adam_kernel(const __grid_constant__ ExchangeAdamArgs a) {
-    twin_barrier(a.g);
-    const long long stride = (long long)gridDim.x * kCommThreads;
+__device__ __forceinline__ void exchange_adam_body(const ExchangeAdamArgs& a, int cta, int n_ctas) {
+    twin_barrier(a.g, cta);
+    const long long stride = (long long)n_ctas * kCommThreads;
     const int world = WORLD > 0 ? WORLD : a.g.world;
     constexpr int U = 2;
-    for (long long i0 = a.g.lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < a.g.hi; i0 += stride * U) {
+    for (long long i0 = a.g.lo + (long long)cta * kCommThreads + threadIdx.x; i0 < a.g.hi; i0 += stride * U) {
         float4 g[U], p[U], m[U], v[U];
         int span[U];
 #pragma unroll
@@ -200,7 +229,15 @@ __global__ void __launch_bounds__(kCommThreads, 2) exchange_adam_kernel(const __
             }
         }
     }
-    twin_barrier(a.g);
+    twin_barrier(a.g, cta);
+}
+
+template <bool MULTICAST, int WORLD>
+__global__ void __launch_bounds__(kCommThreads, 2) exchange_adam_kernel(const __grid_constant__ ExchangeAdamArgs a) {
+    exchange_adam_body<MULTICAST, WORLD>(a, (int)blockIdx.x, (int)gridDim.x);
+}
+__global__ void __launch_bounds__(kCommThreads, 2) exchange_adam_emulated_kernel(const ExchangeAdamArgs* __restrict__ all) {
+    exchange_adam_body<false, 0>(all[blockIdx.y], (int)blockIdx.x, (int)gridDim.x);
 }
 
 void comm_slice(long long n16, int rank, int world, long long* lo, long long* hi) {
@@ -211,8 +248,7 @@ void comm_slice(long long n16, int rank, int world, long long* lo, long long* hi
     *hi = h;
 }
 
-int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas, cudaStream_t s) {
-    CommArgs a;
+static void fill_comm_args(const gsr_peer_group& g, long long numel, CommArgs& a) {
     for (int p = 0; p < GSR_COMM_MAX_PEERS; p++) {
         a.buf[p] = p < g.world ? reinterpret_cast<float4*>(g.buf[p]) : nullptr;
         a.sig[p] = p < g.world ? g.signal[p] : nullptr;
@@ -220,18 +256,28 @@ int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas,
     a.mc = reinterpret_cast<float4*>(g.multicast);
     a.rank = g.rank;
     a.world = g.world;
-    const long long n16 = numel / 4;
-    comm_slice(n16, g.rank, g.world, &a.lo, &a.hi);
-    // the grid must be the same on every rank (CTAs meet their twins): derive it from the largest slice only
+    comm_slice(numel / 4, g.rank, g.world, &a.lo, &a.hi);
+}
+// the grid must be the same on every rank (CTAs meet their twins): derive it from the largest slice only
+static int comm_grid(long long numel, int world, int max_ctas, int per_cta_units, unsigned* grid) {
     int sms = 0;
     { const int e = sm_count(&sms); if (e) return e; }
-    const long long per = (n16 + g.world - 1) / g.world;
-    long long ctas = (per + (long long)kCommThreads * kCommUnroll - 1) / ((long long)kCommThreads * kCommUnroll);
+    const long long n16 = numel / 4;
+    const long long per = (n16 + world - 1) / world;
+    long long ctas = (per + (long long)kCommThreads * per_cta_units - 1) / ((long long)kCommThreads * per_cta_units);
     long long cap = max_ctas > 0 ? max_ctas : 2 * sms;
     if (cap > GSR_COMM_MAX_CTAS) cap = GSR_COMM_MAX_CTAS;
     if (ctas > cap) ctas = cap;
     if (ctas < 1) ctas = 1;
-    const unsigned grid = (unsigned)ctas;
+    *grid = (unsigned)ctas;
+    return 0;
+}
+
+int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas, cudaStream_t s) {
+    CommArgs a;
+    fill_comm_args(g, numel, a);
+    unsigned grid = 1;
+    { const int e = comm_grid(numel, g.world, max_ctas, kCommUnroll, &grid); if (e) return e; }
     if (a.mc != nullptr)
         GSR_LAUNCH("allreduce_sum_multimem", false, s, (allreduce_sum_kernel<true, 0><<<grid, kCommThreads, 0, s>>>(a)));
     else if (g.world == 2)
@@ -245,21 +291,42 @@ int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas,
     return 0;
 }
 
-int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& params, float* exp_avg, float* exp_avg_sq,
-                         const gsr_adam_span* spans, int n_spans, double b1, double b2, double eps, long long numel, int max_ctas,
-                         cudaStream_t s) {
-    ExchangeAdamArgs a;
-    for (int p = 0; p < GSR_COMM_MAX_PEERS; p++) {
-        a.g.buf[p] = p < grads.world ? reinterpret_cast<float4*>(grads.buf[p]) : nullptr;
-        a.g.sig[p] = p < grads.world ? grads.signal[p] : nullptr;
-        a.pbuf[p] = p < params.world ? reinterpret_cast<float4*>(params.buf[p]) : nullptr;
+// All ranks of an emulated group in ONE cooperative launch on the current device (blockIdx.y = rank).
+size_t comm_emulation_scratch_bytes() { return GSR_COMM_MAX_PEERS * (sizeof(ExchangeAdamArgs) > sizeof(CommArgs) ? sizeof(ExchangeAdamArgs) : sizeof(CommArgs)); }
+static int coop_launch(const void* kernel, unsigned grid_x, int world, void* args_dev, cudaStream_t s) {
+    int dev = 0, coop = 0, sms = 0;
+    { const int e = current_device(&dev); if (e) return e; }
+    cudaError_t ce = cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (ce != cudaSuccess) return (int)ce;
+    { const int e = sm_count(&sms); if (e) return e; }
+    if (!coop || (long long)grid_x * world > 2ll * sms) return GSR_E_BADARG;     // every CTA of every rank must be resident
+    void* params[] = {&args_dev};
+    ce = cudaLaunchCooperativeKernel(kernel, dim3(grid_x, (unsigned)world, 1), dim3(kCommThreads, 1, 1), params, 0, s);
+    return (int)ce;
+}
+int launch_allreduce_sum_emulated(const gsr_peer_group* groups, int world, long long numel, int max_ctas, void* scratch_dev,
+                                  cudaStream_t s) {
+    CommArgs host[GSR_COMM_MAX_PEERS];
+    for (int r = 0; r < world; r++) {
+        fill_comm_args(groups[r], numel, host[r]);
+        host[r].mc = nullptr;                                       // one device has no multicast group
     }
-    a.g.mc = reinterpret_cast<float4*>(grads.multicast);
+    unsigned grid = 1;
+    { const int e = comm_grid(numel, world, max_ctas, kCommUnroll, &grid); if (e) return e; }
+    cudaError_t ce = cudaMemcpyAsync(scratch_dev, host, sizeof(CommArgs) * world, cudaMemcpyHostToDevice, s);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);           // `host` lives on this stack frame
+    if (ce != cudaSuccess) return (int)ce;
+    int le = 0;
+    GSR_LAUNCH("allreduce_sum_emulated", false, s, (le = coop_launch((const void*)allreduce_sum_emulated_kernel, grid, world, scratch_dev, s)));
+    return le;
+}
+
+static void fill_exchange_args(const gsr_peer_group& grads, const gsr_peer_group& params, float* exp_avg, float* exp_avg_sq,
+                               const gsr_adam_span* spans, int n_spans, double b1, double b2, double eps, long long numel,
+                               ExchangeAdamArgs& a) {
+    fill_comm_args(grads, numel, a.g);
+    for (int p = 0; p < GSR_COMM_MAX_PEERS; p++) a.pbuf[p] = p < params.world ? reinterpret_cast<float4*>(params.buf[p]) : nullptr;
     a.pmc = reinterpret_cast<float4*>(params.multicast);
-    a.g.rank = grads.rank;
-    a.g.world = grads.world;
-    const long long n16 = numel / 4;
-    comm_slice(n16, grads.rank, grads.world, &a.g.lo, &a.g.hi);
     a.m = reinterpret_cast<float4*>(exp_avg);
     a.v = reinterpret_cast<float4*>(exp_avg_sq);
     a.n_spans = n_spans;
@@ -270,15 +337,15 @@ int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& para
         a.inv_sqrt_bc2[k] = k < n_spans ? spans[k].inv_sqrt_bc2 : 0.f;
     }
     a.h = AdamHyper{(float)(1.0 - b1), (float)b2, (float)(1.0 - b2), (float)eps};
-    int sms = 0;
-    { const int e = sm_count(&sms); if (e) return e; }
-    const long long per = (n16 + grads.world - 1) / grads.world;
-    long long ctas = (per + (long long)kCommThreads * 2 - 1) / ((long long)kCommThreads * 2);
-    long long cap = max_ctas > 0 ? max_ctas : 2 * sms;
-    if (cap > GSR_COMM_MAX_CTAS) cap = GSR_COMM_MAX_CTAS;
-    if (ctas > cap) ctas = cap;
-    if (ctas < 1) ctas = 1;
-    const unsigned grid = (unsigned)ctas;
+}
+
+int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& params, float* exp_avg, float* exp_avg_sq,
+                         const gsr_adam_span* spans, int n_spans, double b1, double b2, double eps, long long numel, int max_ctas,
+                         cudaStream_t s) {
+    ExchangeAdamArgs a;
+    fill_exchange_args(grads, params, exp_avg, exp_avg_sq, spans, n_spans, b1, b2, eps, numel, a);
+    unsigned grid = 1;
+    { const int e = comm_grid(numel, grads.world, max_ctas, 2, &grid); if (e) return e; }
     if (a.g.mc != nullptr)
         GSR_LAUNCH("exchange_adam_multimem", false, s, (exchange_adam_kernel<true, 0><<<grid, kCommThreads, 0, s>>>(a)));
     else if (grads.world == 2)
@@ -290,6 +357,25 @@ int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& para
     else
         GSR_LAUNCH("exchange_adam_peer", false, s, (exchange_adam_kernel<false, 0><<<grid, kCommThreads, 0, s>>>(a)));
     return 0;
+}
+
+int launch_exchange_adam_emulated(const gsr_peer_group* grads, const gsr_peer_group* params, float* const* exp_avg,
+                                  float* const* exp_avg_sq, int world, const gsr_adam_span* spans, int n_spans, double b1, double b2,
+                                  double eps, long long numel, int max_ctas, void* scratch_dev, cudaStream_t s) {
+    static ExchangeAdamArgs host[GSR_COMM_MAX_PEERS];               // too large for the stack of a small thread
+    for (int r = 0; r < world; r++) {
+        fill_exchange_args(grads[r], params[r], exp_avg[r], exp_avg_sq[r], spans, n_spans, b1, b2, eps, numel, host[r]);
+        host[r].g.mc = nullptr;
+        host[r].pmc = nullptr;
+    }
+    unsigned grid = 1;
+    { const int e = comm_grid(numel, world, max_ctas, 2, &grid); if (e) return e; }
+    cudaError_t ce = cudaMemcpyAsync(scratch_dev, host, sizeof(ExchangeAdamArgs) * world, cudaMemcpyHostToDevice, s);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    if (ce != cudaSuccess) return (int)ce;
+    int le = 0;
+    GSR_LAUNCH("exchange_adam_emulated", false, s, (le = coop_launch((const void*)exchange_adam_emulated_kernel, grid, world, scratch_dev, s)));
+    return le;
 }
 
 }  // namespace gsr

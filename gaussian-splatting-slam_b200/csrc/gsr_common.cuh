@@ -93,7 +93,9 @@ static inline bool rect_packing_ok(int W, int H) {
 
 struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46)
     float* depths;            // [P] view-space z (visible Gaussians only)
-    float4* rec;              // [3P] splat records: {x,y,ex,ey} {a,b,c,opacity} {r,g,b,1/depth}
+    float4* rec;              // [2P] cull part of the splat records: {x,y,ex,ey} {a,b,c,opacity} = 32 bytes = one sector per
+                              // Gaussian (everything the sub-tile tests of the blend kernels need)
+    float4* colr;             // [P] colour part: {r,g,b,1/depth} (= rec + 2P; fetched for surviving splats only)
     uint8_t* clamped;         // [P] bit c set = channel c clamped at 0
     uint32_t* tiles_touched;  // [P]
     uint32_t* dkey;           // [P] depth bits (0xFFFFFFFF for culled Gaussians): Gaussian-level sort key
@@ -104,11 +106,13 @@ struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46
     uint32_t* sort_scratch;   // radix-sort tables for the P-sized sort
     unsigned long long* count64;  // [2] instance count of the view (only written when the forward has no capacity estimate)
     uint32_t* rect_packed;    // [P] tile rectangle x0 | y0 << 8 | width << 16 | height << 24 (visible Gaussians; grids up to 255 x 255 tiles)
+    uint32_t* rect_sorted;    // [P] the same words in depth order (written by the scan, read by the instance emission)
     uint32_t* n_visible;      // [1] Gaussians that survived the cull = valid prefix of order / point_offsets (device)
     static GeomState from(char*& p, size_t P) {
         GeomState g;
         g.depths = carve<float>(p, P);
         g.rec = carve<float4>(p, 3 * P);
+        g.colr = g.rec + 2 * P;
         g.clamped = carve<uint8_t>(p, P);
         g.tiles_touched = carve<uint32_t>(p, P);
         g.dkey = carve<uint32_t>(p, P);
@@ -119,6 +123,7 @@ struct GeomState {            // replaces GeometryState (rasterizer_impl.h:31-46
         g.sort_scratch = carve<uint32_t>(p, sort_scratch_words(P));
         g.count64 = carve<unsigned long long>(p, 2);
         g.rect_packed = carve<uint32_t>(p, P);
+        g.rect_sorted = carve<uint32_t>(p, P);
         g.n_visible = g.sort_scratch + 4 * GSR_RADIX + 8;      // where radix_sort_u32's drop mode leaves the kept count
         return g;
     }
@@ -240,6 +245,7 @@ int launch_densify_apply(int P, const void* blob, const gsr_densify_rule* rule, 
 int launch_densify_stats(int P, const float* dL_dmean2D, const uint8_t* update_filter, const int* radii, float* grad_accum,
                          float* denom, float* max_radii2D, cudaStream_t s);
 int set_exact_cull(int on);
+int set_blend_variant(int v);
 int launch_cull_stats(const gsr_view& v, const GeomState& g, const uint32_t* point_list, const ImageState& img,
                       unsigned long long* out, cudaStream_t s);
 int launch_adam(const gsr_adam_group* groups, int n, double b1, double b2, double eps, const uint8_t* visible, cudaStream_t s);
@@ -248,6 +254,12 @@ int launch_exchange_adam(const gsr_peer_group& grads, const gsr_peer_group& para
                          cudaStream_t s);
 int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas, cudaStream_t s);
 void comm_slice(long long n16, int rank, int world, long long* lo, long long* hi);
+size_t comm_emulation_scratch_bytes();
+int launch_allreduce_sum_emulated(const gsr_peer_group* groups, int world, long long numel, int max_ctas, void* scratch_dev,
+                                  cudaStream_t s);
+int launch_exchange_adam_emulated(const gsr_peer_group* grads, const gsr_peer_group* params, float* const* exp_avg,
+                                  float* const* exp_avg_sq, int world, const gsr_adam_span* spans, int n_spans, double b1, double b2,
+                                  double eps, long long numel, int max_ctas, void* scratch_dev, cudaStream_t s);
 int launch_exp_check(unsigned long long* mismatches_dev, cudaStream_t s);
 int launch_fp32_peak(int iters, float* out, int* sms_out, cudaStream_t s);
 int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s);

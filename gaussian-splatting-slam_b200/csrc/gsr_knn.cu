@@ -6,8 +6,12 @@
 //     reference's init = {0,0,0} implies;
 //   * points are COPIED into Morton order once (float4 x,y,z,id) so every later access is a
 //     coalesced stream instead of points[indices[i]] gathers (simple_knn.cu:154-181);
-//   * a CTA of 256 consecutive (spatially coherent) points first prunes boxes against the CTA's own
-//     bounding box, then stages each surviving box in shared memory once for all its threads.
+//   * the search works on TWO box levels: the reference's 1024-point boxes and 64-point sub-boxes. A CTA of 256
+//     consecutive (spatially coherent) points first finds every thread's 3 nearest among the CTA's own points (these are
+//     real candidates, so the pruning radius is tight from the start -- the reference's radius comes from the +-3
+//     neighbours along the Morton curve, simple_knn.cu:157-162, which can be far away), then prunes 1024-point boxes
+//     and their sub-boxes against the CTA's bounding box, stages the surviving sub-boxes four at a time in shared
+//     memory, and every thread scans only those whose box distance beats its current third-best.
 // The result is the exact 3-NN mean, so it equals the reference up to fp32 rounding of d^2.
 #include "gsr_common.cuh"
 #include <cfloat>
@@ -15,6 +19,8 @@
 namespace gsr {
 
 constexpr int kBox = 1024;   // simple_knn.cu:12 BOX_SIZE
+constexpr int kSub = 64;     // points per sub-box
+constexpr int kSubPerBox = kBox / kSub;
 
 struct KnnTemp {
     uint32_t* bbox;        // [8] encoded min xyz (0..2), max xyz (4..6)
@@ -24,6 +30,7 @@ struct KnnTemp {
     uint32_t* idx_tmp;     // [P]
     float4* sorted;        // [P] x,y,z,original id (bits)
     float4* boxes;         // [2*nb] min, max
+    float4* sub;           // [2*nsub] min, max of the 64-point sub-boxes
     uint32_t* sort_scratch;
     static KnnTemp from(char*& p, size_t P) {
         KnnTemp t;
@@ -34,6 +41,7 @@ struct KnnTemp {
         t.idx_tmp = carve<uint32_t>(p, P);
         t.sorted = carve<float4>(p, P);
         t.boxes = carve<float4>(p, 2 * ((P + kBox - 1) / kBox) + 2);
+        t.sub = carve<float4>(p, 2 * ((P + kSub - 1) / kSub) + 2);
         t.sort_scratch = carve<uint32_t>(p, sort_scratch_words(P));
         return t;
     }
@@ -112,12 +120,14 @@ __global__ void __launch_bounds__(256) gather_points_kernel(int P, const float* 
                             __uint_as_float(i));
 }
 
-// one CTA of 256 threads per box of 1024 sorted points (simple_knn.cu:79-118)
-__global__ void __launch_bounds__(256) box_minmax_kernel(int P, const float4* __restrict__ sorted, float4* __restrict__ boxes) {
-    __shared__ float red[6][8];
+// one warp per 64-point sub-box (two points per lane); 8 sub-boxes per CTA
+__global__ void __launch_bounds__(256) sub_minmax_kernel(int P, const float4* __restrict__ sorted, float4* __restrict__ sub) {
+    const int lane = threadIdx.x & 31, sb = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int base = sb * kSub;
+    if (base >= P) return;
     float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    const int base = blockIdx.x * kBox;
-    for (int e = threadIdx.x; e < kBox; e += 256) {
+#pragma unroll
+    for (int e = lane; e < kSub; e += 32) {
         if (base + e < P) {
             const float4 p = __ldg(sorted + base + e);
             mn[0] = fminf(mn[0], p.x); mn[1] = fminf(mn[1], p.y); mn[2] = fminf(mn[2], p.z);
@@ -132,18 +142,26 @@ __global__ void __launch_bounds__(256) box_minmax_kernel(int P, const float4* __
             mx[a] = fmaxf(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
         }
     }
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     if (lane == 0) {
-#pragma unroll
-        for (int a = 0; a < 3; a++) { red[a][w] = mn[a]; red[3 + a][w] = mx[a]; }
+        sub[2 * sb] = make_float4(mn[0], mn[1], mn[2], 0.f);
+        sub[2 * sb + 1] = make_float4(mx[0], mx[1], mx[2], 0.f);
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        for (int k = 1; k < 8; k++)
-            for (int a = 0; a < 3; a++) { mn[a] = fminf(mn[a], red[a][k]); mx[a] = fmaxf(mx[a], red[3 + a][k]); }
-        boxes[2 * blockIdx.x] = make_float4(mn[0], mn[1], mn[2], 0.f);
-        boxes[2 * blockIdx.x + 1] = make_float4(mx[0], mx[1], mx[2], 0.f);
+}
+
+// 1024-point boxes (simple_knn.cu:79-118) from their 16 sub-boxes: one thread per box
+__global__ void __launch_bounds__(256) box_from_sub_kernel(int nb, int nsub, const float4* __restrict__ sub, float4* __restrict__ boxes) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nb) return;
+    float4 mn = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.f), mx = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.f);
+    for (int k = 0; k < kSubPerBox; k++) {
+        const int sb = b * kSubPerBox + k;
+        if (sb >= nsub) break;
+        const float4 a = __ldg(sub + 2 * sb), c = __ldg(sub + 2 * sb + 1);
+        mn.x = fminf(mn.x, a.x); mn.y = fminf(mn.y, a.y); mn.z = fminf(mn.z, a.z);
+        mx.x = fmaxf(mx.x, c.x); mx.y = fmaxf(mx.y, c.y); mx.z = fmaxf(mx.z, c.z);
     }
+    boxes[2 * b] = mn;
+    boxes[2 * b + 1] = mx;
 }
 
 __device__ __forceinline__ void k_best3(const float4& ref, const float4& point, float* knn) {   // simple_knn.cu:132-146
@@ -163,29 +181,41 @@ __device__ __forceinline__ float dist_box_point(const float4& bmin, const float4
     return dx * dx + dy * dy + dz * dz;
 }
 
+// squared gap between two axis-aligned boxes: a lower bound of dist_box_point for every point of the first one
+__device__ __forceinline__ float box_gap2(const float* r, const float4& bmin, const float4& bmax) {
+    const float gx = fmaxf(0.f, fmaxf(bmin.x - r[3], r[0] - bmax.x));
+    const float gy = fmaxf(0.f, fmaxf(bmin.y - r[4], r[1] - bmax.y));
+    const float gz = fmaxf(0.f, fmaxf(bmin.z - r[5], r[2] - bmax.z));
+    return gx * gx + gy * gy + gz * gz;
+}
+
+constexpr int kStage = 4;      // sub-boxes staged per round (kStage * kSub = one point per thread)
 __global__ void __launch_bounds__(256) knn_kernel(int P, const float4* __restrict__ sorted, const float4* __restrict__ boxes,
-                                                   int nb, float* __restrict__ out) {
-    __shared__ float4 s_pts[kBox];
-    __shared__ int s_cand[256];
-    __shared__ int s_ncand;
+                                                   int nb, const float4* __restrict__ sub, int nsub, float* __restrict__ out) {
+    __shared__ float4 s_pts[256];
+    __shared__ float4 s_sb[kStage][2];
+    __shared__ int s_c1[256], s_c0[256];
+    __shared__ int s_n1, s_n0;
     __shared__ float s_red[7][8];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const int pos = blockIdx.x * 256 + tid;
+    const int cbase = blockIdx.x * 256;
+    const int pos = cbase + tid;
     const bool valid = pos < P;
     const float4 me = valid ? __ldg(sorted + pos) : make_float4(0.f, 0.f, 0.f, 0.f);
     float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
-    float reject = 0.f;
+    // ---- phase 1: the CTA's own 256 points (4 sub-boxes), brute force. These are real candidates.
+    const int own = min(256, P - cbase);
+    s_pts[tid] = me;
+    __syncthreads();
     if (valid) {
-        for (int i = max(0, pos - 3); i <= min(P - 1, pos + 3); i++) {   // simple_knn.cu:157-162
-            if (i == pos) continue;
-            k_best3(me, __ldg(sorted + i), best);
+        for (int e = 0; e < own; e++) {
+            if (e == tid) continue;
+            k_best3(me, s_pts[e], best);
         }
-        reject = best[2];
-        best[0] = best[1] = best[2] = FLT_MAX;
     }
-    // CTA bounding box and the largest rejection radius among its points
+    // CTA bounding box and the largest third-best distance among its points
     float r[7] = {valid ? me.x : FLT_MAX, valid ? me.y : FLT_MAX, valid ? me.z : FLT_MAX,
-                  valid ? me.x : -FLT_MAX, valid ? me.y : -FLT_MAX, valid ? me.z : -FLT_MAX, valid ? reject : 0.f};
+                  valid ? me.x : -FLT_MAX, valid ? me.y : -FLT_MAX, valid ? me.z : -FLT_MAX, valid ? best[2] : 0.f};
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
@@ -203,41 +233,54 @@ __global__ void __launch_bounds__(256) knn_kernel(int P, const float4* __restric
         for (int a = 3; a < 7; a++) r[a] = fmaxf(r[a], s_red[a][k]);
     }
     const float rmax = r[6];
+    const int own_sb0 = cbase / kSub, own_sb1 = own_sb0 + 256 / kSub;      // sub-boxes already searched in phase 1
 
+    // ---- phase 2: 1024-point boxes -> their sub-boxes -> points
     for (int c0 = 0; c0 < nb; c0 += 256) {
         __syncthreads();
-        if (tid == 0) s_ncand = 0;
+        if (tid == 0) s_n1 = 0;
         __syncthreads();
         const int b = c0 + tid;
         if (b < nb) {
             const float4 bmin = __ldg(boxes + 2 * b), bmax = __ldg(boxes + 2 * b + 1);
-            // gap between the CTA box and box b: a lower bound of dist_box_point for every thread
-            const float gx = fmaxf(0.f, fmaxf(bmin.x - r[3], r[0] - bmax.x));
-            const float gy = fmaxf(0.f, fmaxf(bmin.y - r[4], r[1] - bmax.y));
-            const float gz = fmaxf(0.f, fmaxf(bmin.z - r[5], r[2] - bmax.z));
-            if (!(gx * gx + gy * gy + gz * gz > rmax)) s_cand[atomicAdd(&s_ncand, 1)] = b;
+            if (!(box_gap2(r, bmin, bmax) > rmax)) s_c1[atomicAdd(&s_n1, 1)] = b;
         }
         __syncthreads();
-        const int ncand = s_ncand;
-        for (int ci = 0; ci < ncand; ci++) {
-            const int bb = s_cand[ci];
-            const float4 bmin = __ldg(boxes + 2 * bb), bmax = __ldg(boxes + 2 * bb + 1);
-            bool want = false;
-            if (valid) {
-                const float d = dist_box_point(bmin, bmax, me);
-                want = !(d > reject || d > best[2]);                       // simple_knn.cu:171-173
-            }
-            if (!__syncthreads_or(want)) continue;
-            const int bbase = bb * kBox, cnt = min(kBox, P - bbase);
-            for (int e = tid; e < cnt; e += 256) s_pts[e] = __ldg(sorted + bbase + e);
+        const int n1 = s_n1;
+        for (int g0 = 0; g0 < n1; g0 += 256 / kSubPerBox) {              // 16 boxes -> 256 sub-boxes, one per thread
             __syncthreads();
-            if (want) {
-                for (int e = 0; e < cnt; e++) {
-                    if (bbase + e == pos) continue;
-                    k_best3(me, s_pts[e], best);
+            if (tid == 0) s_n0 = 0;
+            __syncthreads();
+            const int k = g0 + tid / kSubPerBox;
+            if (k < n1) {
+                const int sb = s_c1[k] * kSubPerBox + (tid % kSubPerBox);
+                if (sb < nsub && (sb < own_sb0 || sb >= own_sb1)) {
+                    const float4 bmin = __ldg(sub + 2 * sb), bmax = __ldg(sub + 2 * sb + 1);
+                    if (!(box_gap2(r, bmin, bmax) > rmax)) s_c0[atomicAdd(&s_n0, 1)] = sb;
                 }
             }
             __syncthreads();
+            const int n0 = s_n0;
+            for (int r0 = 0; r0 < n0; r0 += kStage) {
+                __syncthreads();                                         // the previous round's readers are done
+                const int q = tid / kSub, e = tid % kSub;
+                if (r0 + q < n0) {
+                    const int sb = s_c0[r0 + q];
+                    const int idx = sb * kSub + e;
+                    if (idx < P) s_pts[tid] = __ldg(sorted + idx);
+                    if (e < 2) s_sb[q][e] = __ldg(sub + 2 * sb + e);
+                }
+                __syncthreads();
+                if (valid) {
+                    const int nq = min(kStage, n0 - r0);
+                    for (int qq = 0; qq < nq; qq++) {
+                        const float d = dist_box_point(s_sb[qq][0], s_sb[qq][1], me);
+                        if (d > best[2]) continue;                       // simple_knn.cu:171-173
+                        const int cnt = min(kSub, P - s_c0[r0 + qq] * kSub);
+                        for (int ee = 0; ee < cnt; ee++) k_best3(me, s_pts[qq * kSub + ee], best);
+                    }
+                }
+            }
         }
     }
     if (valid) out[__float_as_uint(me.w)] = (best[0] + best[1] + best[2]) / 3.0f;   // simple_knn.cu:183
@@ -259,9 +302,10 @@ int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s
     if (rc) return rc;
     const uint32_t* sorted_idx = in_a ? t.idx : t.idx_tmp;
     GSR_LAUNCH("knn_gather", false, s, (gather_points_kernel<<<blocks, 256, 0, s>>>(P, pts, sorted_idx, t.sorted)));
-    const int nb = (P + kBox - 1) / kBox;
-    GSR_LAUNCH("knn_boxes", false, s, (box_minmax_kernel<<<nb, 256, 0, s>>>(P, t.sorted, t.boxes)));
-    GSR_LAUNCH("knn_search", false, s, (knn_kernel<<<blocks, 256, 0, s>>>(P, t.sorted, t.boxes, nb, out)));
+    const int nb = (P + kBox - 1) / kBox, nsub = (P + kSub - 1) / kSub;
+    GSR_LAUNCH("knn_subboxes", false, s, (sub_minmax_kernel<<<(nsub + 7) / 8, 256, 0, s>>>(P, t.sorted, t.sub)));
+    GSR_LAUNCH("knn_boxes", false, s, (box_from_sub_kernel<<<(nb + 255) / 256, 256, 0, s>>>(nb, nsub, t.sub, t.boxes)));
+    GSR_LAUNCH("knn_search", false, s, (knn_kernel<<<blocks, 256, 0, s>>>(P, t.sorted, t.boxes, nb, t.sub, nsub, out)));
     return 0;
 }
 

@@ -186,6 +186,7 @@ struct PreArgs {
 template <bool SH16>
 __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a, int* __restrict__ radii,
                                                               float* __restrict__ depths, float4* __restrict__ rec,
+                                                              float4* __restrict__ colr,
                                                               uint8_t* __restrict__ clamped,
                                                               uint32_t* __restrict__ tiles_touched,
                                                               uint32_t* __restrict__ dkey,
@@ -279,9 +280,9 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
 
         my_depth = p_view.z;
         my_radii = my_radius;
-        rec[3 * (size_t)idx + 0] = make_float4(point_image.x, point_image.y, ex, ey);
-        rec[3 * (size_t)idx + 1] = make_float4(conic.x, conic.y, conic.z, opacity);
-        rec[3 * (size_t)idx + 2] = make_float4(color.x, color.y, color.z, 1.0f / p_view.z);
+        rec[2 * (size_t)idx + 0] = make_float4(point_image.x, point_image.y, ex, ey);
+        rec[2 * (size_t)idx + 1] = make_float4(conic.x, conic.y, conic.z, opacity);
+        colr[idx] = make_float4(color.x, color.y, color.z, 1.0f / p_view.z);
         my_clamp = cb;
         my_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
         // the rectangle itself, for the scan and the instance emission (binning): they then need neither the record nor
@@ -753,10 +754,10 @@ int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t 
     uint32_t* tiles_touched = rect_packing_ok(v.W, v.H) ? nullptr : g.tiles_touched;
     if (sh16_fast(v))
         GSR_LAUNCH("preprocess_fwd", v.debug, s,
-                   (preprocess_fwd_kernel<true><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
+                   (preprocess_fwd_kernel<true><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.colr, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
     else
         GSR_LAUNCH("preprocess_fwd", v.debug, s,
-                   (preprocess_fwd_kernel<false><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
+                   (preprocess_fwd_kernel<false><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.colr, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
     return 0;
 }
 

@@ -203,7 +203,11 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
     // predecessor and was a third of the pass
     uint32_t excl = 0;
     if (tile > 0) {
-        constexpr int kLookWin = 8;
+        // 32 predecessors per round trip. The inclusive prefixes advance as a wave front, one window per L2 round trip:
+        // with a window of 8 the last of the depth sort's ~360 concurrently running tiles waited for ~45 round trips
+        // (the four depth passes were pure look-back latency, ~23 us each). The key / value / rank registers are dead
+        // by now (the pairs sit in shared memory), so 32 loads in flight per thread cost no occupancy.
+        constexpr int kLookWin = 32;
         bool done = false;
         for (int j = tile - 1; !done; j -= kLookWin) {
             uint32_t sw[kLookWin];

@@ -373,9 +373,11 @@ def decode_state(P, R, W, H, geomBuffer, binningBuffer, imgBuffer, view_args=Non
     n = L.gsr_geom_layout(C.c_int(P), off, 8)
     go = [off[i] for i in range(n)]
     out["depths"] = take(geomBuffer, go[0], 4 * P, torch.float32, (P,))
-    rec = take(geomBuffer, go[1], 48 * P, torch.float32, (P, 12))
-    out["means2D"], out["extent"] = rec[:, 0:2], rec[:, 2:4]
-    out["conic_opacity"], out["rgb"], out["invdepth_g"] = rec[:, 4:8], rec[:, 8:11], rec[:, 11]
+    # splat records: cull part {x,y,ex,ey}{a,b,c,opacity} as [P,8], then the colour part {r,g,b,1/depth} as [P,4]
+    cull = take(geomBuffer, go[1], 32 * P, torch.float32, (P, 8))
+    colr = take(geomBuffer, go[1] + 32 * P, 16 * P, torch.float32, (P, 4))
+    out["means2D"], out["extent"] = cull[:, 0:2], cull[:, 2:4]
+    out["conic_opacity"], out["rgb"], out["invdepth_g"] = cull[:, 4:8], colr[:, 0:3], colr[:, 3]
     out["clamped"] = take(geomBuffer, go[2], P, torch.uint8, (P,))
     if (W + 15) // 16 <= 255 and (H + 15) // 16 <= 255 and len(go) > 7:
         # grids up to 255 x 255 tiles: the library keeps the packed tile rectangle (x0 | y0 << 8 | w << 16 | h << 24)

@@ -51,6 +51,13 @@ def _gsr():
         L.gsr_comm_slice.argtypes = [C.c_longlong, C.c_int, C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]
         L.gsr_allreduce_sum.restype = C.c_int
         L.gsr_allreduce_sum.argtypes = [C.POINTER(_PeerGroup), C.c_longlong, C.c_int, C.c_void_p]
+        L.gsr_comm_emulation_scratch_bytes.restype = C.c_size_t
+        L.gsr_allreduce_sum_emulated.restype = C.c_int
+        L.gsr_allreduce_sum_emulated.argtypes = [C.POINTER(_PeerGroup), C.c_int, C.c_longlong, C.c_int, C.c_void_p, C.c_void_p]
+        L.gsr_exchange_adam_step_emulated.restype = C.c_int
+        L.gsr_exchange_adam_step_emulated.argtypes = [C.POINTER(_PeerGroup), C.POINTER(_PeerGroup), C.POINTER(C.c_void_p),
+                                                      C.POINTER(C.c_void_p), C.c_int, C.POINTER(_AdamSpan), C.c_int, C.c_double,
+                                                      C.c_double, C.c_double, C.c_longlong, C.c_int, C.c_void_p, C.c_void_p]
         L._comm_bound = True
     return L, _C
 
@@ -68,6 +75,44 @@ def peer_all_reduce(group_desc: "_PeerGroup", numel: int, max_ctas: int = 0, str
     L, _C = _gsr()
     st = torch.cuda.current_stream().cuda_stream if stream is None else stream
     _C._check(L.gsr_allreduce_sum(C.byref(group_desc), numel, max_ctas, C.c_void_p(st)), "gsr_allreduce_sum")
+
+
+def _emulation_scratch(device):
+    L, _ = _gsr()
+    return torch.empty(int(L.gsr_comm_emulation_scratch_bytes()), dtype=torch.uint8, device=device)
+
+
+def emulated_all_reduce(groups, numel: int, max_ctas: int = 0, stream=None):
+    """Tests without a second GPU: every rank of an EMULATED group (all buffers and pads on the current device) in ONE
+    cooperative launch -- kernels that wait for one another must never be separate launches on one GPU."""
+    L, _C = _gsr()
+    world = len(groups)
+    arr = (_PeerGroup * world)(*groups)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    scratch = _emulation_scratch(dev)
+    st = torch.cuda.current_stream().cuda_stream if stream is None else stream
+    _C._check(L.gsr_allreduce_sum_emulated(arr, world, numel, max_ctas, C.c_void_p(scratch.data_ptr()), C.c_void_p(st)),
+              "gsr_allreduce_sum_emulated")
+    torch.cuda.current_stream().synchronize()       # scratch must outlive the launch
+
+
+def emulated_exchange_adam(grads, params, exp_avg, exp_avg_sq, spans, beta1, beta2, eps, numel, max_ctas: int = 0):
+    """gsr_exchange_adam_step for all ranks of an emulated group in one cooperative launch (see emulated_all_reduce)."""
+    L, _C = _gsr()
+    world = len(grads)
+    ga, pa = (_PeerGroup * world)(*grads), (_PeerGroup * world)(*params)
+    ma = (C.c_void_p * world)(*[t.data_ptr() for t in exp_avg])
+    va = (C.c_void_p * world)(*[t.data_ptr() for t in exp_avg_sq])
+    arr = (_AdamSpan * max(1, len(spans)))()
+    for k, (b, e, ss, ib) in enumerate(spans):
+        arr[k] = _AdamSpan(int(b), int(e), float(ss), float(ib))
+    dev = torch.device("cuda", torch.cuda.current_device())
+    scratch = _emulation_scratch(dev)
+    st = torch.cuda.current_stream().cuda_stream
+    _C._check(L.gsr_exchange_adam_step_emulated(ga, pa, ma, va, world, arr, len(spans), beta1, beta2, eps, numel, max_ctas,
+                                                C.c_void_p(scratch.data_ptr()), C.c_void_p(st)),
+              "gsr_exchange_adam_step_emulated")
+    torch.cuda.current_stream().synchronize()
 
 
 class PeerExchange:

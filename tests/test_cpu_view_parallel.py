@@ -107,7 +107,7 @@ def test_comm_slices_partition_the_bucket_and_bad_arguments_are_refused(gsr_lib)
     assert L.gsr_comm_slice(6, 0, 2, C.byref(lo), C.byref(hi)) == -1          # not a multiple of 4
     assert L.gsr_comm_slice(8, 2, 2, C.byref(lo), C.byref(hi)) == -1          # rank outside the group
     assert L.gsr_comm_slice(8, 0, 17, C.byref(lo), C.byref(hi)) == -1         # more peers than GSR_COMM_MAX_PEERS
-    assert L.gsr_comm_signal_bytes() == 4 * 512 * 16
+    assert L.gsr_comm_signal_bytes() == 4 * (512 * 16 + 16)               # slots + the error area
     g = _PeerGroup()
     g.rank, g.world = 0, 2
     assert L.gsr_allreduce_sum(C.byref(g), 1024, 0, None) == -1               # NULL peer mappings

@@ -1,15 +1,17 @@
 """GPU tests (-m gpu) of the peer-memory gradient exchange (csrc/gsr_comm.cu) on ONE device: the "ranks"
-are buffers and signal pads on the same GPU and their kernels run concurrently on separate streams, so the twin
+are buffers and signal pads on the same GPU, and ALL of them run in ONE cooperative launch (blockIdx.y = rank,
+gsr_allreduce_sum_emulated / gsr_exchange_adam_step_emulated: the same device code as the per-rank kernels). Separate
+launches that wait for one another are not guaranteed to be resident together, so they are never used. The twin
 barriers, the slice ownership and the rank-ordered summation are exercised exactly as across NVLink (the multicast
-variant needs a real NVSwitch group: tools/comm_check.py under torchrun covers it). Oracle: the sum in rank order,
-computed by torch on the same device, bit for bit."""
+variant needs a real NVSwitch group: tests/test_gpu_multirank.py and tools/comm_check.py under torchrun cover it).
+Oracle: the sum in rank order, computed by torch on the same device, bit for bit."""
 import ctypes as C
 import math
 
 import pytest
 import torch
 
-from view_parallel import _PeerGroup, comm_slice, peer_all_reduce, _gsr
+from view_parallel import _PeerGroup, comm_slice, emulated_all_reduce, emulated_exchange_adam, peer_all_reduce, _gsr
 
 pytestmark = pytest.mark.gpu
 
@@ -32,19 +34,20 @@ def test_emulated_ranks_on_one_device_sum_in_rank_order(world, numel, max_ctas):
     gen = torch.Generator(device=dev).manual_seed(world * 1000 + numel % 997)
     bufs = [torch.randn(numel, device=dev, generator=gen) * (10.0 ** (r % 3)) for r in range(world)]
     pads = [torch.zeros(L.gsr_comm_signal_bytes() // 4, dtype=torch.int32, device=dev) for _ in range(world)]
-    streams = [torch.cuda.Stream(dev) for _ in range(world)]
     torch.cuda.synchronize()
     for rep in range(3):                                        # the pads reset themselves: the launch is repeatable
         want = bufs[0].clone()
         for r in range(1, world):
             want = want + bufs[r]                               # rank order, fp32, round to nearest
-        # all ranks' CTAs must be co-resident (they wait for their twins): max_ctas x world stays far below 2 x 148
-        for r in range(world):
-            peer_all_reduce(_group(bufs, pads, r), numel, max_ctas, stream=streams[r].cuda_stream)
+        if world == 1:
+            peer_all_reduce(_group(bufs, pads, 0), numel, max_ctas)       # a single rank waits for nobody
+        else:
+            # one cooperative launch for all ranks: max_ctas x world stays far below 2 x 148 resident CTAs
+            emulated_all_reduce([_group(bufs, pads, r) for r in range(world)], numel, max_ctas)
         torch.cuda.synchronize()
         for r in range(world):
             assert torch.equal(bufs[r], want), f"rank {r} rep {rep}: max diff {(bufs[r] - want).abs().max().item()}"
-        assert all(int(p.abs().sum()) == 0 for p in pads)       # every signal consumed
+        assert all(int(p.abs().sum()) == 0 for p in pads)       # every signal consumed, no error word set
 
 
 def test_slices_match_the_kernel_ownership():
@@ -61,7 +64,6 @@ def test_exchange_adam_on_emulated_ranks_equals_allreduce_then_adam(world, sizes
     bucket. Parameters on every rank and the moment slices must match bit for bit, over two consecutive steps; the
     gradient buckets stay untouched; alignment padding between the parameter spans is left alone."""
     import gsr_optim
-    from view_parallel import exchange_adam_raw
     L, _ = _gsr()
     dev = torch.device("cuda:0")
     gen = torch.Generator(device=dev).manual_seed(world)
@@ -78,7 +80,6 @@ def test_exchange_adam_on_emulated_ranks_equals_allreduce_then_adam(world, sizes
     ms = [torch.zeros(max(hi - lo, 4), device=dev) for lo, hi in slices]
     vs = [torch.zeros(max(hi - lo, 4), device=dev) for lo, hi in slices]
     ref_p, ref_m, ref_v = p0.clone(), torch.zeros(numel, device=dev), torch.zeros(numel, device=dev)
-    streams = [torch.cuda.Stream(dev) for _ in range(world)]
     b1, b2, eps = 0.9, 0.999, 1e-15
     for t in (1, 2):
         gbufs = [torch.randn(numel, device=dev, generator=gen) * (0.1 + r) for r in range(world)]
@@ -92,9 +93,8 @@ def test_exchange_adam_on_emulated_ranks_equals_allreduce_then_adam(world, sizes
         spans = [(o, o + n, lr / (1 - b1 ** t), 1 / math.sqrt(1 - b2 ** t)) for o, n, lr in zip(offs, sizes, lrs)]
         gsr_optim.adam_step_raw([(ref_p[b:e], gsum[b:e], ref_m[b:e], ref_v[b:e], 1, ss, ib) for b, e, ss, ib in spans], b1, b2, eps)
         torch.cuda.synchronize()
-        for r in range(world):
-            exchange_adam_raw(_group(gbufs, pads, r), _group(pbufs, pads, r), ms[r], vs[r], spans, b1, b2, eps, numel,
-                              max_ctas, stream=streams[r].cuda_stream)
+        emulated_exchange_adam([_group(gbufs, pads, r) for r in range(world)], [_group(pbufs, pads, r) for r in range(world)],
+                               ms, vs, spans, b1, b2, eps, numel, max_ctas)
         torch.cuda.synchronize()
         for r in range(world):
             assert torch.equal(pbufs[r], ref_p), f"step {t} rank {r}: max diff {(pbufs[r] - ref_p).abs().max().item()}"
