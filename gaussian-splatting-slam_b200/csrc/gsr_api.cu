@@ -199,6 +199,7 @@ struct CapHint { int dev, W, H; double per_gaussian; double high; };
 std::mutex g_hint_mu;
 std::vector<CapHint> g_hints;
 int g_speculate = -1;                        // -1: read GSR_SPECULATE on first use
+int g_overlap = 1;                           // tile table on a side stream under the depth sort (gsr_set_speculation(2) = off)
 unsigned long long g_spec_hits = 0, g_spec_retries = 0, g_spec_cold = 0;
 
 bool speculation_on() {
@@ -216,7 +217,7 @@ uint32_t hint_capacity(int dev, int W, int H, int P) {
             // map raises the count with it); 1/8 headroom, rounded up to whole sort tiles
             double c = std::max(h.high, h.per_gaussian * (double)P) * 1.125 + 8192.0;
             if (c > 1.0e9) c = 1.0e9;
-            return (uint32_t)(((size_t)c + GSR_SORT_TILE - 1) / GSR_SORT_TILE * GSR_SORT_TILE);
+            return (uint32_t)(((size_t)c + 4095) / 4096 * 4096);
         }
     return 0;
 }
@@ -240,6 +241,22 @@ struct CountSlot {
     unsigned long long* host64 = nullptr;
     cudaEvent_t ev[kMaxDevices] = {};
     bool have[kMaxDevices] = {};
+    cudaStream_t side_stream[kMaxDevices] = {};
+    cudaEvent_t fork_ev[kMaxDevices] = {}, join_ev[kMaxDevices] = {};
+    int side_state[kMaxDevices] = {};      // 0 = not created, 1 = ready, -1 = creation failed (stay in-stream)
+    int side(int dev, cudaStream_t* st, cudaEvent_t* fork, cudaEvent_t* join) {
+        if (dev < 0 || dev >= kMaxDevices) return GSR_E_BADARG;
+        if (side_state[dev] == 0) {
+            cudaError_t ce = cudaStreamCreateWithFlags(&side_stream[dev], cudaStreamNonBlocking);
+            if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&fork_ev[dev], cudaEventDisableTiming);
+            if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&join_ev[dev], cudaEventDisableTiming);
+            side_state[dev] = ce == cudaSuccess ? 1 : -1;
+            if (ce != cudaSuccess) (void)cudaGetLastError();
+        }
+        if (side_state[dev] != 1) return GSR_E_BADARG;
+        *st = side_stream[dev]; *fork = fork_ev[dev]; *join = join_ev[dev];
+        return 0;
+    }
     int get(int dev, cudaEvent_t* e) {
         if (!host) {
             void* p = nullptr;
@@ -261,7 +278,7 @@ struct CountSlot {
 thread_local CountSlot t_slot;
 }  // namespace
 
-int gsr_set_speculation(int on) { g_speculate = on ? 1 : 0; return 0; }
+int gsr_set_speculation(int on) { g_speculate = on ? 1 : 0; g_overlap = on == 2 ? 0 : 1; return 0; }
 int gsr_reset_capacity_hints(void) {
     std::lock_guard<std::mutex> lk(g_hint_mu);
     g_hints.clear();
@@ -301,15 +318,38 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
     cudaEvent_t ev;
     e = t_slot.get(dev, &ev);
     if (e) return e;
-    e = launch_preprocess(v, g, radii, s);
-    if (e) return e;
-    e = launch_depth_order(v, g, s);
-    if (e) return e;
-
     constexpr uint32_t kLimit = (1u << 30) - 1u;                      // saturation value of the scan
     uint32_t cap = speculation_on() ? hint_capacity(dev, v.W, v.H, v.P) : 0u;
+    if (cap >= kLimit) cap = kLimit - 1u;
     uint32_t R = 0;
     const bool cold = cap == 0u;
+    e = launch_preprocess(v, g, radii, s);
+    if (e) return e;
+    // With a capacity estimate the binning blob exists already, and the tile table -- which needs the preprocess only --
+    // runs on a side stream UNDER the depth sort (four latency-bound passes that leave most of the GPU idle).
+    char* bp = nullptr;
+    bool table_done = false;
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    if (!cold && g_overlap && !v.debug && t_slot.side(dev, &side, &ev_fork, &ev_join) == 0) {
+        bp = binning_alloc(binning_ctx, blob_size_binning((size_t)cap, (size_t)v.P, v.W, v.H));
+        if (!bp) return GSR_E_ALLOC;
+        BinningState b0 = BinningState::from(bp, (size_t)cap, (size_t)v.P, v.W, v.H);
+        cudaError_t ce = cudaEventRecord(ev_fork, s);
+        if (ce == cudaSuccess) ce = cudaStreamWaitEvent(side, ev_fork, 0);
+        if (ce != cudaSuccess) return (int)ce;
+        e = launch_tile_table(v, g, radii, b0, img, side);
+        if (e) return e;
+        ce = cudaEventRecord(ev_join, side);
+        if (ce != cudaSuccess) return (int)ce;
+        table_done = true;
+    }
+    e = launch_depth_order(v, g, s);
+    if (e) return e;
+    if (table_done) {
+        cudaError_t ce = cudaStreamWaitEvent(s, ev_join, 0);
+        if (ce != cudaSuccess) return (int)ce;
+    }
     if (cold) {
         // no estimate for this image size yet: count first (rasterizer_impl.cu:281, the reference's one host synchronisation)
         g_spec_cold++;
@@ -322,12 +362,19 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
         R = (uint32_t)*t_slot.host64;
         cap = R;
     }
-    if (cap >= kLimit) cap = kLimit - 1u;
     for (int attempt = 0; attempt < 2; attempt++) {
-        char* bp = binning_alloc(binning_ctx, blob_size_binning((size_t)cap, (size_t)v.P, v.W, v.H));
-        if (!bp) return GSR_E_ALLOC;
+        if (!bp) {
+            bp = binning_alloc(binning_ctx, blob_size_binning((size_t)cap, (size_t)v.P, v.W, v.H));
+            if (!bp) return GSR_E_ALLOC;
+        }
         BinningState b = BinningState::from(bp, (size_t)cap, (size_t)v.P, v.W, v.H);
+        bp = nullptr;                                                 // a repeat allocates a new blob
         uint32_t* total_dev = nullptr;
+        if (!table_done) {
+            e = launch_tile_table(v, g, radii, b, img, s);
+            if (e) return e;
+        }
+        table_done = false;
         e = launch_binning(v, g, radii, b, img, cap, &total_dev, s);
         if (e) return e;
         if (!cold || attempt > 0 || v.debug) {                        // the count goes home while the rest is being queued
@@ -374,7 +421,7 @@ int gsr_backward(const gsr_view* view, int R, const int* radii, const char* geom
     ImageState img = ImageState::from(ip, (size_t)v.W * v.H, (size_t)tiles_of(v.W, v.H));
     char* ap = accum_scratch;
     float* acc = carve<float>(ap, (size_t)v.P * GSR_ACC_FLOATS);
-    GSR_MEMSET("memset_grad_acc", s, acc, 0, sizeof(float) * GSR_ACC_FLOATS * (size_t)v.P);
+    if (!out->accum_clean) GSR_MEMSET("memset_grad_acc", s, acc, 0, sizeof(float) * GSR_ACC_FLOATS * (size_t)v.P);
     int e = 0;
     if (R > 0) {
         e = launch_blend_backward(v, g, BinningState::point_list_of(binning), img, dL_dpix, dL_dinvdepth, acc, s);

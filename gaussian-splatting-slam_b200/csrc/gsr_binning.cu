@@ -18,8 +18,8 @@ namespace gsr {
 
 // ------------------------------------------------------------------ scan + emission (A6 + A7)
 constexpr int kScanThreads = 256;
-constexpr int kScanItems = GSR_SCAN_TILE / kScanThreads;   // 4, blocked per thread
-static_assert(kScanItems == 4, "scan_emit_kernel loads its four ids with one 16-byte request");
+constexpr int kScanItems = GSR_SCAN_TILE / kScanThreads;   // 8, blocked per thread
+static_assert(kScanItems % 4 == 0, "scan_offsets_kernel loads its ids with 16-byte requests");
 
 __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* warp_sums, uint32_t& total) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -53,13 +53,12 @@ __device__ __forceinline__ void rect_of(float px, float py, int max_radius, int 
 }
 
 // Replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:277): single-pass chained scan (decoupled look-back) of
-// the tile counts in DEPTH order. A CTA takes 1024 visible Gaussians by ticket (which makes waiting on lower-numbered
-// tiles safe whatever the CTA scheduling order), gathers their packed rectangles through `order` (L2 hits: 4 B x P),
-// scans locally, publishes its sum and looks back with ALL its threads (1024 predecessors per round trip). A tile's
+// the tile counts in DEPTH order. CTA b takes the b-th 2048 visible Gaussians, gathers their packed rectangles through
+// `order` (L2 hits: 4 B x P), scans locally, publishes its sum and looks back with ALL its threads (1024 predecessors per round trip). A tile's
 // status word carries flag (bits 30-31: 1 = the tile's own sum, 2 = inclusive prefix) and value (30 bits, saturating)
 // together, so one 32-bit store publishes both. status[0..m) = tile words (all inclusive prefixes once the kernel has
 // finished: the emission uses them as the first level of its search), status[m_slots] = grand total,
-// status[m_slots + 1] = ticket; all zeroed before the launch. The rectangles are also written out in depth order.
+// status[m_slots + 2] = the tile table's arrival counter; all zeroed before the launch. The rectangles are also written out in depth order.
 constexpr uint32_t kScanOwn = 1u << 30, kScanIncl = 2u << 30, kScanVal = (1u << 30) - 1u;
 template <bool PACKED>
 __global__ void __launch_bounds__(kScanThreads) scan_offsets_kernel(const uint32_t* __restrict__ n_dev,
@@ -71,20 +70,24 @@ __global__ void __launch_bounds__(kScanThreads) scan_offsets_kernel(const uint32
     // n (visible Gaussians, in depth order) lives on the device; the grid covers the host's upper bound and m_slots only
     // fixes where the total and the ticket sit. CTAs whose ticket lies beyond the last tile leave at once.
     __shared__ uint32_t warp_sums[kScanThreads / 32];
-    __shared__ uint32_t s_tile;
     __shared__ unsigned long long s_part[kScanThreads / 32];
     __shared__ int s_found[kScanThreads / 32];
-    if (threadIdx.x == 0) s_tile = atomicAdd(status + m_slots + 1, 1u);
-    __syncthreads();
-    const int tile = (int)s_tile;
+    // CTA b scans tile b: it only ever waits for lower-numbered tiles, whose CTAs were dispatched before it. (A ticket
+    // per tile costs a same-address atomic, and those serialise in L2 at ~20 ns each: 2930 CTAs -> the whole kernel.)
+    const int tile = (int)blockIdx.x;
     const int n = (int)__ldg(n_dev);
     const int m = (n + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE;
     if (tile >= m) return;
     const int base = tile * GSR_SCAN_TILE + threadIdx.x * kScanItems;
-    uint32_t g[kScanItems] = {0u, 0u, 0u, 0u}, c[kScanItems], v = 0;
+    uint32_t g[kScanItems], c[kScanItems], v = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) g[i] = 0u;
     if (base + kScanItems <= n) {
-        const uint4 o4 = __ldg(reinterpret_cast<const uint4*>(order + base));     // base is a multiple of 4, order 128-byte aligned
-        g[0] = o4.x; g[1] = o4.y; g[2] = o4.z; g[3] = o4.w;
+#pragma unroll
+        for (int q = 0; q < kScanItems / 4; q++) {      // base is a multiple of 4, order 128-byte aligned
+            const uint4 o4 = __ldg(reinterpret_cast<const uint4*>(order + base) + q);
+            g[4 * q] = o4.x; g[4 * q + 1] = o4.y; g[4 * q + 2] = o4.z; g[4 * q + 3] = o4.w;
+        }
     } else {
 #pragma unroll
         for (int i = 0; i < kScanItems; i++)
@@ -158,12 +161,12 @@ __global__ void __launch_bounds__(kScanThreads) scan_offsets_kernel(const uint32
 // slots, whatever number of Gaussians they belong to. (Emitting per Gaussian -- the reference's mapping, one thread per
 // Gaussian -- leaves the near Gaussians, which cover hundreds of tiles each and come first in depth order, to a few
 // threads while the rest of the GPU idles.) The CTA finds the Gaussians that own its slots in two cooperative steps,
-// both counts over sorted arrays: the scan's per-1024 inclusive prefixes give the first and last scan tile, the offsets
+// both counts over sorted arrays: the scan's per-tile inclusive prefixes give the first and last scan tile, the offsets
 // of those two tiles the first and last Gaussian. Their offsets / ids / rectangles (<= 4097 of each) are staged in shared
 // memory; a slot's owner is the number of range ends at or before it: the ends are strictly increasing, so they are
 // distinct bits of a 4096-bit map, and the owner is a prefix popcount. Stores are coalesced, writes clamped to `cap`.
 constexpr int kEmitThreads = 256;
-constexpr int kEmitTile = GSR_SORT_TILE;                    // 4096 slots per CTA = one tile of the instance sort
+constexpr int kEmitTile = 4096;                             // slots per CTA
 constexpr int kEmitMax = kEmitTile + 8;                     // Gaussians a CTA can need (4097), padded
 template <bool PACKED>
 __global__ void __launch_bounds__(kEmitThreads) emit_instances_kernel(const uint32_t* __restrict__ n_dev,
@@ -480,21 +483,16 @@ static int bits_for(uint32_t count) {   // bits needed to represent ids 0..count
     return b;
 }
 
-int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, uint32_t cap,
-                   uint32_t** total_dev, cudaStream_t s) {
+// Clears the binning blob's tables and builds the tile table (ranges + the instance sort's histograms). Depends on the
+// preprocess only, so gsr_forward runs it on a side stream under the depth sort.
+int launch_tile_table(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, cudaStream_t s) {
     const int gx = (v.W + GSR_TILE - 1) / GSR_TILE, gy = (v.H + GSR_TILE - 1) / GSR_TILE;
     const int tiles = gx * gy;
     const int tbits = bits_for((uint32_t)tiles);
     const int passes = radix_passes(tbits);
     if (passes > 4) return GSR_E_TOOLARGE;
     const int m = (int)BinningState::scan_tiles((size_t)v.P);
-    *total_dev = b.scan_sums + m;
     GSR_MEMSET("memset_binning", s, b.zero_begin, 0, (size_t)(b.zero_end - b.zero_begin));
-    // make the sorted result land in point_list
-    uint32_t *ka = b.tile_keys, *va = b.point_list, *kb = b.tile_keys_tmp, *vb = b.vals_tmp;
-    if (passes % 2) { ka = b.tile_keys_tmp; va = b.vals_tmp; kb = b.tile_keys; vb = b.point_list; }
-    // tile table first: it streams the packed rectangles (12 MB at 3M Gaussians), which leaves them in L2 for the scan's
-    // gather through `order`
     {
         const size_t table_bytes = BinningState::diff_cells(v.W, v.H) * sizeof(int32_t);
         const int use_smem = table_bytes <= (size_t)kTableSmemMax ? 1 : 0;
@@ -517,6 +515,22 @@ int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningSta
                            b.sort_scratch)));
         }
     }
+    return 0;
+}
+
+int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, uint32_t cap,
+                   uint32_t** total_dev, cudaStream_t s) {
+    (void)img;
+    const int gx = (v.W + GSR_TILE - 1) / GSR_TILE, gy = (v.H + GSR_TILE - 1) / GSR_TILE;
+    const int tiles = gx * gy;
+    const int tbits = bits_for((uint32_t)tiles);
+    const int passes = radix_passes(tbits);
+    if (passes > 4) return GSR_E_TOOLARGE;
+    const int m = (int)BinningState::scan_tiles((size_t)v.P);
+    *total_dev = b.scan_sums + m;
+    // make the sorted result land in point_list
+    uint32_t *ka = b.tile_keys, *va = b.point_list, *kb = b.tile_keys_tmp, *vb = b.vals_tmp;
+    if (passes % 2) { ka = b.tile_keys_tmp; va = b.vals_tmp; kb = b.tile_keys; vb = b.point_list; }
     if (cap > 0) {
         const int emit_blocks = (int)((cap + (uint32_t)kEmitTile - 1) / (uint32_t)kEmitTile);
         static DeviceOnce once_ep, once_eu;

@@ -76,9 +76,11 @@ static inline T* carve(char*& p, size_t count) {
     return r;
 }
 
+#ifndef GSR_SORT_TILE
 #define GSR_SORT_TILE 4096    // keys per radix-sort tile (256 threads x 16)
+#endif
 #define GSR_RADIX 256
-#define GSR_SCAN_TILE 1024    // items per scan tile (256 threads x 4)
+#define GSR_SCAN_TILE 2048    // items per scan tile (256 threads x 8): 3M Gaussians, half of them visible -> one wave of CTAs
 
 static inline size_t sort_tiles(size_t n) { return (n + GSR_SORT_TILE - 1) / GSR_SORT_TILE; }
 // scratch words for radix_sort_u32 over n items: digit histograms [4][256], tickets, and one look-back status
@@ -204,17 +206,20 @@ int launch_depth_order(const gsr_view& v, GeomState& g, cudaStream_t s);
 // number of instances = sum of the tile counts (only used when the forward has no capacity estimate yet); *total_dev
 // points at the device word
 int launch_count_instances(const gsr_view& v, GeomState& g, cudaStream_t s);
-// scan of the tile counts in depth order + instance emission (one kernel), tile table (ranges + digit histograms from the
-// rectangles' difference array), stable sort by tile id. `cap` = instances the binning blob holds; the real count lands
-// in *total_dev (device). Safe for any count: writes are clamped to cap, and a count above cap turns the later stages
-// (sort passes, forward blend) into no-ops so that the caller can repeat the call with a larger blob.
+// clears the binning blob's tables and builds the tile table (ranges + digit histograms from the rectangles' difference
+// array); needs the preprocess only
+int launch_tile_table(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, cudaStream_t s);
+// after launch_tile_table on the same blob: scan of the tile counts in depth order, instance emission, stable sort by tile
+// id. `cap` = instances the binning blob holds; the real count lands in *total_dev (device). Safe for any count: writes
+// are clamped to cap, and a count above cap turns the later stages (sort passes, forward blend) into no-ops so that the
+// caller can repeat the call with a larger blob.
 int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img,
                    uint32_t cap, uint32_t** total_dev, cudaStream_t s);
 int launch_blend_forward(const gsr_view& v, const GeomState& g, const uint32_t* point_list, ImageState& img,
                          float* out_color, float* out_invdepth, const uint32_t* total_dev, uint32_t cap, cudaStream_t s);
 int launch_blend_backward(const gsr_view& v, const GeomState& g, const uint32_t* point_list, const ImageState& img,
                           const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s);
-int launch_preprocess_backward(const gsr_view& v, const GeomState& g, const int* radii, const float* acc,
+int launch_preprocess_backward(const gsr_view& v, const GeomState& g, const int* radii, float* acc,
                                bool have_invdepth, const gsr_grads& out, cudaStream_t s);
 // Stable LSD radix sort of (u32 key, u32 value) pairs on key bits [0, total_bits). Ping-pongs between
 // (ka,va) and (kb,vb); *result_in_a tells where the sorted data ended up. scratch: sort_scratch_words(n).

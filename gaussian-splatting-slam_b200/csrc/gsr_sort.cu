@@ -22,6 +22,7 @@ namespace gsr {
 
 constexpr int kSortThreads = 256;
 constexpr int kSortItems = GSR_SORT_TILE / kSortThreads;   // 16
+constexpr int kSortCtasPerSm = GSR_SORT_TILE >= 4096 ? 3 : 5;
 constexpr int kSortWarps = kSortThreads / 32;               // 8
 constexpr uint32_t kFlagAgg = 1u << 30, kFlagInc = 2u << 30, kValMask = (1u << 30) - 1u;
 constexpr unsigned kAll = 0xffffffffu;
@@ -80,15 +81,23 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const uint32_t
     const int nvec = n >> 2;                                       // keys is 128-byte aligned (carved scratch)
     const uint4* k4 = reinterpret_cast<const uint4*>(keys);
     const int stride = gridDim.x * kSortThreads;
-    for (int i = blockIdx.x * kSortThreads + t; i < nvec; i += stride) {
-        const uint4 v = __ldg(k4 + i);
-        const uint32_t kk[4] = {v.x, v.y, v.z, v.w};
+    constexpr int kU = 4;                                          // 16-byte loads in flight per thread
+    for (int i0 = blockIdx.x * kSortThreads + t; i0 < nvec; i0 += stride * kU) {
+        uint4 v[kU];
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            if (drop && kk[j] == 0xFFFFFFFFu) continue;            // dropped keys are in no histogram
-            for (int p = 0; p < passes; p++) {
-                const int bits = min(8, total_bits - 8 * p);
-                atomicAdd(&sh[p][cp][(kk[j] >> (8 * p)) & ((1u << bits) - 1u)], 1u);
+        for (int u = 0; u < kU; u++)
+            v[u] = (i0 + u * stride < nvec) ? __ldg(k4 + i0 + u * stride) : make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            if (i0 + u * stride >= nvec) continue;
+            const uint32_t kk[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                if (drop && kk[j] == 0xFFFFFFFFu) continue;        // dropped keys are in no histogram
+                for (int p = 0; p < passes; p++) {
+                    const int bits = min(8, total_bits - 8 * p);
+                    atomicAdd(&sh[p][cp][(kk[j] >> (8 * p)) & ((1u << bits) - 1u)], 1u);
+                }
             }
         }
     }
@@ -203,11 +212,10 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
     // predecessor and was a third of the pass
     uint32_t excl = 0;
     if (tile > 0) {
-        // 32 predecessors per round trip. The inclusive prefixes advance as a wave front, one window per L2 round trip:
-        // with a window of 8 the last of the depth sort's ~360 concurrently running tiles waited for ~45 round trips
-        // (the four depth passes were pure look-back latency, ~23 us each). The key / value / rank registers are dead
-        // by now (the pairs sit in shared memory), so 32 loads in flight per thread cost no occupancy.
-        constexpr int kLookWin = 32;
+        // (measured and not adopted: a window of 32 -- most tiles find an inclusive prefix among their nearest predecessors,
+        // the 24 extra status loads per thread are pure L2 traffic; CTA b = tile b without tickets when the grid covers all
+        // tiles, and the next ticket requested before the ranking and consumed after it -- both a few per cent slower)
+        constexpr int kLookWin = 8;
         bool done = false;
         for (int j = tile - 1; !done; j -= kLookWin) {
             uint32_t sw[kLookWin];
@@ -253,7 +261,7 @@ __device__ __forceinline__ void onesweep_tile(SortSmem& sm, const uint32_t (&key
 // WRITE_KEYS = false: the last pass of the instance sort leaves the keys unwritten (nobody reads sorted tile ids: the
 // tile ranges come from the tile table).
 template <int BITS, int MODE, bool WRITE_KEYS>
-__global__ void __launch_bounds__(kSortThreads, 3) onesweep_kernel(const uint32_t* __restrict__ keys_in,
+__global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm) onesweep_kernel(const uint32_t* __restrict__ keys_in,
                                                                     const uint32_t* __restrict__ vals_in,
                                                                     uint32_t* __restrict__ keys_out,
                                                                     uint32_t* __restrict__ vals_out, int n, int n_tiles,
@@ -319,7 +327,7 @@ static int launch_pass(const uint32_t* kin, const uint32_t* vin, uint32_t* kout,
     int sms = 148;
     e = sm_count(&sms);
     if (e) return e;
-    const int ctas = tiles < sms * 3 ? tiles : sms * 3;
+    const int ctas = tiles < sms * kSortCtasPerSm ? tiles : sms * kSortCtasPerSm;
     onesweep_kernel<BITS, MODE, WRITE_KEYS><<<ctas, kSortThreads, sizeof(SortSmem), s>>>(kin, vin, kout, vout, n, tiles, shift, ghist, ticket, status, n_valid_out, n_dev);
     return 0;
 }
@@ -370,7 +378,9 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
         // should see at least ~16K keys; 4 CTAs per SM at most
         int sms = 148;
         { const int se = sm_count(&sms); if (se) return se; }
-        const int hist_blocks = min((n + 16383) / 16384, sms * 4);
+        // few CTAs: every CTA ends with up to 1024 global atomics on the same 1024 counters, and same-address atomics
+    // serialise in L2 (~20 ns each) -- at 4 CTAs per SM that flush alone cost 12 us
+    const int hist_blocks = min((n + 16383) / 16384, sms);
         GSR_LAUNCH("radix_hist", debug, s,
                    (radix_hist_kernel<<<hist_blocks > 0 ? hist_blocks : 1, kSortThreads, 0, s>>>(ka, n, passes, total_bits, ghist, drop ? 1 : 0)));
     }

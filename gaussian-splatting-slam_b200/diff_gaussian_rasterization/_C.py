@@ -10,7 +10,7 @@ import os
 import torch
 
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-_LIB_PATH = os.path.join(_PKG_ROOT, "libgsr.so")
+_LIB_PATH = os.environ.get("GSR_LIB") or os.path.join(_PKG_ROOT, "libgsr.so")      # GSR_LIB: an experimental build (build.py --variant)
 
 
 class _View(C.Structure):
@@ -24,11 +24,35 @@ class _View(C.Structure):
 class _Grads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("dL_dmeans2D", "dL_dopacity", "dL_dmeans3D", "dL_dcolors", "dL_dcov3D",
                                           "dL_dsh", "dL_dscales", "dL_drotations", "dL_dconic", "dL_ddc")] + \
-               [("accumulate", C.c_int)]
+               [("accumulate", C.c_int), ("accum_clean", C.c_int)]
 
 
 _ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
 _lib = None
+_ext = None         # the compiled torch binding (csrc/torch_binding.cpp -> _gsr_torch.so), False when absent / disabled
+
+
+def torch_ext():
+    """The thin PyTorch C++ extension over the same C ABI, preferred for the three hot entry points when it has been
+    built (build.py builds it next to libgsr.so): one pybind transition per call instead of ~60 Python-level operations.
+    GSR_BINDING=ctypes forces the ctypes binding below; both call the same gsr_forward / gsr_backward."""
+    global _ext
+    if _ext is None:
+        _ext = False
+        if os.environ.get("GSR_BINDING", "").lower() != "ctypes" and not os.environ.get("GSR_LIB"):
+            path = os.path.join(_PKG_ROOT, "_gsr_torch.so")
+            if os.path.exists(path):
+                import importlib.util
+                lib()                                   # libgsr.so first: the extension links it
+                spec = importlib.util.spec_from_file_location("_gsr_torch", path)
+                m = importlib.util.module_from_spec(spec)
+                spec.loader.exec_module(m)
+                _ext = m
+    return _ext
+
+
+def binding_name():
+    return "torch-extension" if torch_ext() else "ctypes"
 
 
 def lib():
@@ -80,6 +104,9 @@ def lib():
     return _lib
 
 
+_EMPTY = torch.empty(0)
+
+
 def _check(code, what):
     if code != 0:
         raise RuntimeError(f"{what}: {lib().gsr_error_string(code).decode()} (code {code})")
@@ -116,6 +143,7 @@ def _round_capacity(nbytes):
     return nbytes
 
 
+_acc_clean = {}     # (device index, stream id, P) -> zero-filled accumulator of the backward (kept all zero by the library)
 _pool = {}          # (device index, stream id) -> free scratch tensors
 _DEBUG_POOL = os.environ.get("GSR_DEBUG_POOL", "0") == "1"
 _POOL_MAX = 12
@@ -166,6 +194,9 @@ class ScratchLease:
 def empty_scratch_pool():
     """Drops every pooled scratch buffer (the torch caching allocator gets the memory back)."""
     _pool.clear()
+    _acc_clean.clear()
+    if torch_ext():
+        torch_ext().drop_cached_scratch()
 
 
 class _Scratch:
@@ -236,6 +267,13 @@ def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_m
     if means3D.ndim != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")   # rasterize_points.cu:57-59
     _dev(means3D, "means3D")
+    ext = torch_ext()
+    if ext:
+        n, color, radii, geom, binning, image, invdepth = ext.rasterize_gaussians(
+            bg, means3D, colors, opacity, scales, rotations, float(scale_modifier), cov3D_precomp, viewmatrix, projmatrix,
+            float(tan_fovx), float(tan_fovy), int(image_height), int(image_width), sh, int(degree), campos, bool(prefiltered),
+            bool(debug), bool(antialiasing), bool(want_invdepth), dc if dc is not None else _EMPTY)
+        return n, color, radii, geom, binning, image, (invdepth if want_invdepth else None)
     H, W, P = int(image_height), int(image_width), int(means3D.size(0))
     dev = means3D.device
     with torch.cuda.device(dev):
@@ -271,6 +309,22 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
     "opacities", "shs" | "colors_precomp", "scales" + "rotations" | "cov3D_precomp"), one for EVERY supplied input. The
     gradients of this view are then ADDED into them inside the kernel (gsr_grads.accumulate) and the corresponding
     returned entries are None; dL_dmeans2D is still returned per view."""
+    ext = torch_ext()
+    if ext:
+        has_dc = dc is not None and dc.numel() != 0
+        sinks = []
+        if grad_sinks is not None:
+            sinks = [grad_sinks.get(k) for k in ("means3D", "opacities", "colors_precomp", "cov3D_precomp", "shs", "scales",
+                                                 "rotations", "dc")]
+        res = ext.rasterize_gaussians_backward(
+            bg, means3D, radii, colors, opacity, scales, rotations, float(scale_modifier), cov3D_precomp, viewmatrix,
+            projmatrix, float(tan_fovx), float(tan_fovy), dL_dout_color, dL_dout_invdepth, sh, int(degree), campos, geomBuffer,
+            int(R), binningBuffer, imageBuffer, bool(antialiasing), bool(debug), bool(want_conic), grad_sinks is not None, sinks,
+            dc if dc is not None else _EMPTY)
+        out = tuple(res[:8])
+        if want_conic:
+            out = out + (res[8],)
+        return out + (res[9],) if has_dc else out
     P = int(means3D.size(0))
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     dev = means3D.device
@@ -307,16 +361,25 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
         dL_dmeans3D, dL_dopacity, dL_dcolors, dL_dcov3D = o["means3D"], o["opacities"], o["colors_precomp"], o["cov3D_precomp"]
         dL_dsh, dL_dscales, dL_drot, dL_ddc = o["shs"], o["scales"], o["rotations"], o["dc"]
         if P != 0:
-            g = _Grads(_ptr(dL_dmeans2D), _ptr(dL_dopacity), _ptr(dL_dmeans3D), _ptr(dL_dcolors), _ptr(dL_dcov3D),
-                       _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot), _ptr(dL_dconic), _ptr(dL_ddc),
-                       0 if grad_sinks is None else 1)
             dpix = _f32(dL_dout_color)
             dinv = _f32(dL_dout_invdepth) if dL_dout_invdepth is not None else None
-            nacc = int(lib().gsr_backward_scratch_bytes(P))
-            acc = lease.take(dev, nacc) if lease is not None else torch.empty(nacc, dtype=torch.uint8, device=dev)
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            # The packed gradient accumulator (48 B per Gaussian) is kept per (device, stream, P) and stays ALL ZERO between
+            # calls: the backward zeroes the rows it read (gsr_grads.accum_clean), so no clear per view.
+            key = (dev.index, stream, P)
+            acc = _acc_clean.get(key)
+            if acc is None:
+                if len(_acc_clean) >= 8:
+                    _acc_clean.clear()
+                acc = torch.zeros(int(lib().gsr_backward_scratch_bytes(P)), dtype=torch.uint8, device=dev)
+                _acc_clean[key] = acc
+            g = _Grads(_ptr(dL_dmeans2D), _ptr(dL_dopacity), _ptr(dL_dmeans3D), _ptr(dL_dcolors), _ptr(dL_dcov3D),
+                       _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot), _ptr(dL_dconic), _ptr(dL_ddc),
+                       0 if grad_sinks is None else 1, 1)
             rc = lib().gsr_backward(C.byref(view), int(R), _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
-                                    _ptr(imageBuffer), dpix.data_ptr(), _ptr(dinv), acc.data_ptr(), C.byref(g),
-                                    torch.cuda.current_stream(dev).cuda_stream)
+                                    _ptr(imageBuffer), dpix.data_ptr(), _ptr(dinv), acc.data_ptr(), C.byref(g), stream)
+            if rc != 0:
+                _acc_clean.pop(key, None)               # possibly dirty now
             _check(rc, "gsr_backward")
     if grad_sinks is not None:
         dL_dcolors = dL_dopacity = dL_dmeans3D = dL_dcov3D = dL_dsh = dL_dscales = dL_drot = dL_ddc = None
@@ -329,6 +392,9 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
 def mark_visible(means3D, viewmatrix, projmatrix):
     """rasterize_points.cu:198-217"""
     _dev(means3D, "means3D")
+    ext = torch_ext()
+    if ext:
+        return ext.mark_visible(means3D, viewmatrix, projmatrix)
     P = int(means3D.size(0))
     dev = means3D.device
     present = torch.zeros((P,), dtype=torch.bool, device=dev)
