@@ -710,6 +710,7 @@ def _main(out_fd):
                "d2h_bytes_per_step": d2h, "timing": "host wall clock around K steps incl. pinned H2D/D2H, max over ranks"}
 
     spec_stats = arm._C.speculation_stats() if args.impl == "ours" else None
+    binding = arm._C.binding_name() if args.impl == "ours" else "reference pybind module (oracle/_ref/ref_dgr_C.so)"
     fp32_peak = None
     if rank == 0 and args.impl == "ours":
         try:
@@ -750,7 +751,7 @@ def _main(out_fd):
                                          (f", one {exchange_desc} of 59 floats/Gaussian per step" if ref_world > 1 else ""),
                           "l2": "inputs (708 MB parameters + 300 MB scratch per view) exceed the 126 MB L2; no explicit flush"},
                "step_ms_min_med_max": [round(step_ms[0], 3), round(step_ms[len(step_ms) // 2], 3), round(step_ms[-1], 3)],
-               "clocks": clocks, "gpu_launches": launches,
+               "clocks": clocks, "gpu_launches": launches, "binding": binding,
                "host": {"cpus_usable": len(os.sched_getaffinity(0)), "cpus_total": os.cpu_count(),
                         "rank0_bound_to_gpu_numa_cpus": (f"{bound_cpus[0]}-{bound_cpus[-1]} ({len(bound_cpus)})" if bound_cpus else None)},
                "kernel_timing_pass_ms_per_step": round(ms_prof / args.steps, 3) if ms_prof else None}

@@ -167,6 +167,7 @@ def run_small(args, dev, emit, out_fd, ClockSampler, local):
                                "sample": "unmodified reference CUDA rasterizer / simple-knn (oracle/_ref) on one B200, same step"}
     else:
         out["kernels"] = kernels
+        out["binding"] = arm._C.binding_name()
         if args.workload != "c2":
             out["speculation"] = dict(zip(("estimate_held", "repeated", "counted_first"), arm._C.speculation_stats()))
     emit(out_fd, out)

@@ -1,6 +1,7 @@
 // gsr_api.cu -- the extern "C" boundary declared in include/gsr.h and the stage orchestration that
 // replaces CudaRasterizer::Rasterizer::forward / backward (rasterizer_impl.cu:198-336, 340-434).
 #include "gsr_common.cuh"
+#include <nvtx3/nvToolsExt.h>
 #include <cstdio>
 #include <cstring>
 #include <algorithm>
@@ -28,6 +29,13 @@ cudaEvent_t prof_event() {
     return e;
 }
 }  // namespace
+static bool nvtx_env() {
+    const char* e = getenv("GSR_NVTX");
+    return e && e[0] == '1';
+}
+bool g_nvtx_on = nvtx_env();
+void nvtx_push(const char* what) { nvtxRangePushA(what); }
+void nvtx_pop() { nvtxRangePop(); }
 void prof_begin(const char* what, cudaStream_t s) {
     ProfRec r{what, prof_event(), prof_event()};
     cudaEventRecord(r.a, s);
@@ -107,6 +115,8 @@ int gsr_key_bits(int W, int H) { return 32 + (int)higher_msb((uint32_t)tiles_of(
 size_t gsr_backward_scratch_bytes(int P) { return sizeof(float) * GSR_ACC_FLOATS * (size_t)(P > 0 ? P : 0) + 256; }
 size_t gsr_dist2_temp_bytes(int P) { return dist2_temp_bytes(P); }
 uint64_t gsr_launch_count(void) { return g_launches; }
+
+int gsr_nvtx_enable(int on) { g_nvtx_on = on != 0; return 0; }
 
 int gsr_profile_enable(int on) {
     if (on) {   // a new recording starts: recycle the previous log's events
@@ -237,7 +247,8 @@ void hint_update(int dev, int W, int H, int P, uint32_t R) {
 
 // pinned word + event for the count's way home (one per host thread: gsr_forward waits before it returns)
 struct CountSlot {
-    uint32_t* host = nullptr;
+    uint32_t* host = nullptr;                // pinned + mapped: the scan kernel stores num_rendered here
+    uint32_t* host_dev = nullptr;            // ... through this device pointer
     unsigned long long* host64 = nullptr;
     cudaEvent_t ev[kMaxDevices] = {};
     bool have[kMaxDevices] = {};
@@ -260,9 +271,13 @@ struct CountSlot {
     int get(int dev, cudaEvent_t* e) {
         if (!host) {
             void* p = nullptr;
-            cudaError_t ce = cudaHostAlloc(&p, 64, cudaHostAllocPortable);
+            cudaError_t ce = cudaHostAlloc(&p, 64, cudaHostAllocPortable | cudaHostAllocMapped);
+            if (ce != cudaSuccess) return (int)ce;
+            void* dp = nullptr;
+            ce = cudaHostGetDevicePointer(&dp, p, 0);
             if (ce != cudaSuccess) return (int)ce;
             host = reinterpret_cast<uint32_t*>(p);
+            host_dev = reinterpret_cast<uint32_t*>(dp);
             host64 = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(p) + 16);
         }
         if (dev < 0 || dev >= kMaxDevices) return GSR_E_BADARG;
@@ -290,9 +305,18 @@ int gsr_speculation_stats(unsigned long long* out3) {
     return 0;
 }
 
+namespace {
+struct NvtxScope {
+    bool on;
+    explicit NvtxScope(const char* name) : on(g_nvtx_on) { if (on) nvtx_push(name); }
+    ~NvtxScope() { if (on) nvtx_pop(); }
+};
+}  // namespace
+
 int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, gsr_alloc_fn binning_alloc,
                 void* binning_ctx, gsr_alloc_fn image_alloc, void* image_ctx, float* out_color, int* radii,
                 float* out_invdepth, int* num_rendered, void* stream) {
+    NvtxScope nvtx_scope("gsr_forward");
     if (!view_ok(view) || !geom_alloc || !binning_alloc || !image_alloc || !out_color || !num_rendered) return GSR_E_BADARG;
     const gsr_view& v = *view;
     cudaStream_t s = (cudaStream_t)stream;
@@ -323,28 +347,38 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
     if (cap >= kLimit) cap = kLimit - 1u;
     uint32_t R = 0;
     const bool cold = cap == 0u;
-    e = launch_preprocess(v, g, radii, s);
-    if (e) return e;
-    // With a capacity estimate the binning blob exists already, and the tile table -- which needs the preprocess only --
-    // runs on a side stream UNDER the depth sort (four latency-bound passes that leave most of the GPU idle).
+    // With a capacity estimate the binning blob exists before the first kernel: the preprocess clears the tables of the
+    // depth sort and of the binning on the side (no memset launches), and the tile table -- which needs the preprocess
+    // only -- runs on a side stream UNDER the depth sort (four latency-bound passes that leave most of the GPU idle).
     char* bp = nullptr;
-    bool table_done = false;
-    cudaStream_t side = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    if (!cold && g_overlap && !v.debug && t_slot.side(dev, &side, &ev_fork, &ev_join) == 0) {
+    bool table_done = false, binning_zeroed = false;
+    cudaEvent_t ev_join = nullptr;
+    void* za = nullptr; size_t zan = 0;
+    depth_sort_zero_region(g, &za, &zan);
+    if (!cold) {
         bp = binning_alloc(binning_ctx, blob_size_binning((size_t)cap, (size_t)v.P, v.W, v.H));
         if (!bp) return GSR_E_ALLOC;
         BinningState b0 = BinningState::from(bp, (size_t)cap, (size_t)v.P, v.W, v.H);
-        cudaError_t ce = cudaEventRecord(ev_fork, s);
-        if (ce == cudaSuccess) ce = cudaStreamWaitEvent(side, ev_fork, 0);
-        if (ce != cudaSuccess) return (int)ce;
-        e = launch_tile_table(v, g, radii, b0, img, side);
+        e = launch_preprocess(v, g, radii, s, za, zan, b0.zero_begin, (size_t)(b0.zero_end - b0.zero_begin));
         if (e) return e;
-        ce = cudaEventRecord(ev_join, side);
-        if (ce != cudaSuccess) return (int)ce;
-        table_done = true;
+        binning_zeroed = true;
+        cudaStream_t side = nullptr;
+        cudaEvent_t ev_fork = nullptr;
+        if (g_overlap && !v.debug && t_slot.side(dev, &side, &ev_fork, &ev_join) == 0) {
+            cudaError_t ce = cudaEventRecord(ev_fork, s);
+            if (ce == cudaSuccess) ce = cudaStreamWaitEvent(side, ev_fork, 0);
+            if (ce != cudaSuccess) return (int)ce;
+            e = launch_tile_table(v, g, radii, b0, img, side, /*scratch_zeroed=*/true);
+            if (e) return e;
+            ce = cudaEventRecord(ev_join, side);
+            if (ce != cudaSuccess) return (int)ce;
+            table_done = true;
+        }
+    } else {
+        e = launch_preprocess(v, g, radii, s, za, zan);
+        if (e) return e;
     }
-    e = launch_depth_order(v, g, s);
+    e = launch_depth_order(v, g, s, /*scratch_zeroed=*/true);
     if (e) return e;
     if (table_done) {
         cudaError_t ce = cudaStreamWaitEvent(s, ev_join, 0);
@@ -371,23 +405,33 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
         bp = nullptr;                                                 // a repeat allocates a new blob
         uint32_t* total_dev = nullptr;
         if (!table_done) {
-            e = launch_tile_table(v, g, radii, b, img, s);
+            e = launch_tile_table(v, g, radii, b, img, s, binning_zeroed);
             if (e) return e;
         }
         table_done = false;
-        e = launch_binning(v, g, radii, b, img, cap, &total_dev, s);
+        binning_zeroed = false;                                       // a repeat works on a fresh blob
+        const bool check_count = !cold || attempt > 0 || v.debug;
+        constexpr uint32_t kPending = 0xFFFFFFFFu;
+        if (check_count) *(volatile uint32_t*)t_slot.host = kPending;
+        e = launch_binning(v, g, radii, b, img, cap, &total_dev, check_count && cap > 0 ? t_slot.host_dev : nullptr, s);
         if (e) return e;
-        if (!cold || attempt > 0 || v.debug) {                        // the count goes home while the rest is being queued
-            cudaError_t ce = cudaMemcpyAsync(t_slot.host, total_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, s);
-            if (ce == cudaSuccess) ce = cudaEventRecord(ev, s);
-            if (ce != cudaSuccess) return (int)ce;
-        }
         e = launch_blend_forward(v, g, b.point_list, img, out_color, out_invdepth, cold && attempt == 0 ? nullptr : total_dev, cap, s);
         if (e) return e;
-        if (cold && attempt == 0 && !v.debug) break;                  // exact capacity: nothing to check
-        cudaError_t ce = cudaEventSynchronize(ev);                    // waits for the emission kernel only; the sort and the
-        if (ce != cudaSuccess) return (int)ce;                        // blend queued behind it keep the GPU busy
-        const uint32_t got = *t_slot.host;
+        if (!check_count) break;                                      // exact capacity: nothing to check
+        // The count leaves the device from inside the scan kernel (a store into mapped pinned memory): the host waits for
+        // that kernel only, while the emission, the sort and the blend queued behind it keep the GPU busy.
+        uint32_t got = cap > 0 ? *(volatile uint32_t*)t_slot.host : 0u;
+        for (unsigned spins = 0; got == kPending; spins++) {
+            if ((spins & 1023u) == 1023u) {
+                const cudaError_t q = cudaStreamQuery(s);
+                if (q != cudaErrorNotReady) {                         // the stream has drained (or failed): one last look
+                    got = *(volatile uint32_t*)t_slot.host;
+                    if (got == kPending) return q != cudaSuccess ? (int)q : GSR_E_BADARG;
+                    break;
+                }
+            }
+            got = *(volatile uint32_t*)t_slot.host;
+        }
         if (cold && attempt == 0) {                                   // debug mode: the two counts must agree
             if (got != R) return GSR_E_BADARG;
             break;
@@ -406,6 +450,7 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
 
 int gsr_backward(const gsr_view* view, int R, const int* radii, const char* geom, const char* binning, const char* image,
                  const float* dL_dpix, const float* dL_dinvdepth, char* accum_scratch, const gsr_grads* out, void* stream) {
+    NvtxScope nvtx_scope("gsr_backward");
     if (!view_ok(view) || !out) return GSR_E_BADARG;
     const gsr_view& v = *view;
     if (v.P == 0) return 0;

@@ -66,7 +66,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_offsets_kernel(const uint32
                                                                      const uint32_t* __restrict__ counts, int m_slots,
                                                                      uint32_t* __restrict__ status,
                                                                      uint32_t* __restrict__ point_offsets,
-                                                                     uint32_t* __restrict__ rect_sorted) {
+                                                                     uint32_t* __restrict__ rect_sorted,
+                                                                     uint32_t* __restrict__ host_total) {
     // n (visible Gaussians, in depth order) lives on the device; the grid covers the host's upper bound and m_slots only
     // fixes where the total and the ticket sit. CTAs whose ticket lies beyond the last tile leave at once.
     __shared__ uint32_t warp_sums[kScanThreads / 32];
@@ -77,7 +78,11 @@ __global__ void __launch_bounds__(kScanThreads) scan_offsets_kernel(const uint32
     const int tile = (int)blockIdx.x;
     const int n = (int)__ldg(n_dev);
     const int m = (n + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE;
-    if (tile >= m) return;
+    if (tile >= m) {
+        // nothing visible at all: the count (0) still has to reach the host, which polls host_total (mapped pinned memory)
+        if (m == 0 && tile == 0 && threadIdx.x == 0 && host_total != nullptr) { *host_total = 0u; __threadfence_system(); }
+        return;
+    }
     const int base = tile * GSR_SCAN_TILE + threadIdx.x * kScanItems;
     uint32_t g[kScanItems], c[kScanItems], v = 0;
 #pragma unroll
@@ -147,7 +152,11 @@ __global__ void __launch_bounds__(kScanThreads) scan_offsets_kernel(const uint32
         const unsigned long long incl_sum = prefix + total;
         const uint32_t sat = incl_sum >= kScanVal ? kScanVal : (uint32_t)incl_sum;
         if (tile > 0) vs[tile] = kScanIncl | sat;
-        if (tile == m - 1) status[m_slots] = sat;
+        if (tile == m - 1) {
+            status[m_slots] = sat;
+            // the count goes home from here: a store into mapped pinned memory, no copy operation behind the sort passes
+            if (host_total != nullptr) { *host_total = sat; __threadfence_system(); }
+        }
     }
     uint32_t run = ex + (prefix >= kScanVal ? kScanVal : (uint32_t)prefix);
 #pragma unroll
@@ -306,12 +315,20 @@ int launch_count_instances(const gsr_view& v, GeomState& g, cudaStream_t s) {
     return 0;
 }
 
-int launch_depth_order(const gsr_view& v, GeomState& g, cudaStream_t s) {
+// the depth sort's tables and the instance counter are carved next to each other: one region to clear
+void depth_sort_zero_region(GeomState& g, void** begin, size_t* bytes) {
+    *begin = g.sort_scratch;
+    *bytes = (size_t)(reinterpret_cast<const char*>(g.count64 + 2) - reinterpret_cast<const char*>(g.sort_scratch));
+}
+
+int launch_depth_order(const gsr_view& v, GeomState& g, cudaStream_t s, bool scratch_zeroed) {
     const int P = v.P;
     bool in_a = true;
-    // one memset clears the depth sort's tables and the instance counter: they are carved next to each other
-    const char* zero_end = reinterpret_cast<const char*>(g.count64 + 2);
-    GSR_MEMSET("memset_depth_sort", s, g.sort_scratch, 0, (size_t)(zero_end - reinterpret_cast<const char*>(g.sort_scratch)));
+    if (!scratch_zeroed) {
+        void* zb; size_t zn;
+        depth_sort_zero_region(g, &zb, &zn);
+        GSR_MEMSET("memset_depth_sort", s, zb, 0, zn);
+    }
     uint32_t* n_vis = nullptr;
     int e = radix_sort_u32(g.dkey, g.order, g.dkey_tmp, g.order_tmp, P, 32, g.sort_scratch, &in_a, v.debug != 0, s, &n_vis,
                            /*scratch_zeroed=*/true);
@@ -485,14 +502,15 @@ static int bits_for(uint32_t count) {   // bits needed to represent ids 0..count
 
 // Clears the binning blob's tables and builds the tile table (ranges + the instance sort's histograms). Depends on the
 // preprocess only, so gsr_forward runs it on a side stream under the depth sort.
-int launch_tile_table(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, cudaStream_t s) {
+int launch_tile_table(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, cudaStream_t s,
+                      bool scratch_zeroed) {
     const int gx = (v.W + GSR_TILE - 1) / GSR_TILE, gy = (v.H + GSR_TILE - 1) / GSR_TILE;
     const int tiles = gx * gy;
     const int tbits = bits_for((uint32_t)tiles);
     const int passes = radix_passes(tbits);
     if (passes > 4) return GSR_E_TOOLARGE;
     const int m = (int)BinningState::scan_tiles((size_t)v.P);
-    GSR_MEMSET("memset_binning", s, b.zero_begin, 0, (size_t)(b.zero_end - b.zero_begin));
+    if (!scratch_zeroed) GSR_MEMSET("memset_binning", s, b.zero_begin, 0, (size_t)(b.zero_end - b.zero_begin));
     {
         const size_t table_bytes = BinningState::diff_cells(v.W, v.H) * sizeof(int32_t);
         const int use_smem = table_bytes <= (size_t)kTableSmemMax ? 1 : 0;
@@ -519,7 +537,7 @@ int launch_tile_table(const gsr_view& v, GeomState& g, const int* radii, Binning
 }
 
 int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, uint32_t cap,
-                   uint32_t** total_dev, cudaStream_t s) {
+                   uint32_t** total_dev, uint32_t* host_total, cudaStream_t s) {
     (void)img;
     const int gx = (v.W + GSR_TILE - 1) / GSR_TILE, gy = (v.H + GSR_TILE - 1) / GSR_TILE;
     const int tiles = gx * gy;
@@ -539,7 +557,7 @@ int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningSta
             { const int e = ensure_dynamic_smem(emit_instances_kernel<true>, (int)smem, once_ep); if (e) return e; }
             GSR_LAUNCH("scan_offsets", v.debug, s,
                        (scan_offsets_kernel<true><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.rect_packed, m, b.scan_sums,
-                                                                            g.point_offsets, g.rect_sorted)));
+                                                                            g.point_offsets, g.rect_sorted, host_total)));
             GSR_LAUNCH("emit_instances", v.debug, s,
                        (emit_instances_kernel<true><<<emit_blocks, kEmitThreads, smem, s>>>(
                            g.n_visible, b.scan_sums, m, g.point_offsets, g.order, g.rect_sorted, g.rec, radii, gx, gy, cap, ka, va)));
@@ -548,7 +566,7 @@ int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningSta
             { const int e = ensure_dynamic_smem(emit_instances_kernel<false>, (int)smem, once_eu); if (e) return e; }
             GSR_LAUNCH("scan_offsets", v.debug, s,
                        (scan_offsets_kernel<false><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.tiles_touched, m, b.scan_sums,
-                                                                             g.point_offsets, nullptr)));
+                                                                             g.point_offsets, nullptr, host_total)));
             GSR_LAUNCH("emit_instances", v.debug, s,
                        (emit_instances_kernel<false><<<emit_blocks, kEmitThreads, smem, s>>>(
                            g.n_visible, b.scan_sums, m, g.point_offsets, g.order, nullptr, g.rec, radii, gx, gy, cap, ka, va)));

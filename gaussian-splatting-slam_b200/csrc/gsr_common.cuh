@@ -16,11 +16,18 @@ extern bool g_prof_on;                               // gsr_profile_enable(): CU
 int check_launch(const char* what, bool debug, cudaStream_t s);
 void prof_begin(const char* what, cudaStream_t s);
 void prof_end(cudaStream_t s);
+// NVTX: with GSR_NVTX=1 in the environment (or gsr_nvtx_enable(1)) every launch sits inside a named range, so nsys / ncu
+// group the kernels by stage as the reference's iter_start / iter_end events do per iteration (train.py:60-61,87,139).
+extern bool g_nvtx_on;
+void nvtx_push(const char* what);
+void nvtx_pop();
 #define GSR_LAUNCH(what, debug, stream, ...)                 \
     do {                                                     \
+        if (gsr::g_nvtx_on) gsr::nvtx_push(what);            \
         if (gsr::g_prof_on) gsr::prof_begin(what, stream);   \
         __VA_ARGS__;                                         \
         if (gsr::g_prof_on) gsr::prof_end(stream);           \
+        if (gsr::g_nvtx_on) gsr::nvtx_pop();                 \
         gsr::g_launches++;                                   \
         int _e = gsr::check_launch(what, debug, stream);     \
         if (_e) return _e;                                   \
@@ -199,22 +206,27 @@ static inline uint32_t higher_msb(uint32_t n) {   // rasterizer_impl.cu:35-50
 #define GSR_ACC_FLOATS 12
 
 // ---------------------------------------------------------------- stage entry points (host)
-int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s);
+// zero_a / zero_b: optional scratch regions (multiples of 4 bytes) the kernel zero-fills on the side
+int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s, void* zero_a = nullptr,
+                      size_t zero_a_bytes = 0, void* zero_b = nullptr, size_t zero_b_bytes = 0);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s);
 // depth-order the visible Gaussians (drop-mode radix sort; the visible count stays on the device)
-int launch_depth_order(const gsr_view& v, GeomState& g, cudaStream_t s);
+int launch_depth_order(const gsr_view& v, GeomState& g, cudaStream_t s, bool scratch_zeroed = false);
+void depth_sort_zero_region(GeomState& g, void** begin, size_t* bytes);
 // number of instances = sum of the tile counts (only used when the forward has no capacity estimate yet); *total_dev
 // points at the device word
 int launch_count_instances(const gsr_view& v, GeomState& g, cudaStream_t s);
 // clears the binning blob's tables and builds the tile table (ranges + digit histograms from the rectangles' difference
 // array); needs the preprocess only
-int launch_tile_table(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, cudaStream_t s);
+int launch_tile_table(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, cudaStream_t s,
+                      bool scratch_zeroed = false);
 // after launch_tile_table on the same blob: scan of the tile counts in depth order, instance emission, stable sort by tile
 // id. `cap` = instances the binning blob holds; the real count lands in *total_dev (device). Safe for any count: writes
 // are clamped to cap, and a count above cap turns the later stages (sort passes, forward blend) into no-ops so that the
 // caller can repeat the call with a larger blob.
+// host_total: NULL, or mapped pinned host memory the scan's last tile stores the count into (the host polls it).
 int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img,
-                   uint32_t cap, uint32_t** total_dev, cudaStream_t s);
+                   uint32_t cap, uint32_t** total_dev, uint32_t* host_total, cudaStream_t s);
 int launch_blend_forward(const gsr_view& v, const GeomState& g, const uint32_t* point_list, ImageState& img,
                          float* out_color, float* out_invdepth, const uint32_t* total_dev, uint32_t cap, cudaStream_t s);
 int launch_blend_backward(const gsr_view& v, const GeomState& g, const uint32_t* point_list, const ImageState& img,

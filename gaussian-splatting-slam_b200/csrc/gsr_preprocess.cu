@@ -181,6 +181,11 @@ struct PreArgs {
     int prefiltered, antialiasing;
     const float *means3D, *shs, *sh_dc, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
     const float *view, *proj, *campos;   // device pointers (16, 16, 3 floats)
+    // Scratch tables the later stages need zero-filled (depth sort: histograms, tickets, look-back status; binning: the
+    // same for the instance sort + scan words + difference array). The forward preprocess clears them on the side --
+    // a fraction of a word per thread -- instead of two memset launches in front of latency-bound kernels.
+    uint32_t* zero_a; long long zero_a_words;
+    uint32_t* zero_b; long long zero_b_words;
 };
 
 template <bool SH16>
@@ -193,6 +198,11 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
                                                               uint32_t* __restrict__ order,
                                                               uint32_t* __restrict__ rect_packed) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    {
+        const long long nthreads = (long long)gridDim.x * blockDim.x;
+        for (long long w = idx; w < a.zero_a_words; w += nthreads) a.zero_a[w] = 0u;
+        for (long long w = idx; w < a.zero_b_words; w += nthreads) a.zero_b[w] = 0u;
+    }
     if (idx >= a.P) return;
     int my_radii = 0;
     uint32_t my_tiles = 0, my_key = 0xFFFFFFFFu;   // culled Gaussians sort to the end and emit nothing
@@ -318,6 +328,7 @@ static void fill_pre_args(const gsr_view& v, PreArgs& a) {
     a.means3D = v.means3D; a.shs = v.shs; a.sh_dc = v.sh_dc; a.colors_precomp = v.colors_precomp; a.opacities = v.opacities;
     a.scales = v.scales; a.rotations = v.rotations; a.cov3D_precomp = v.cov3D_precomp;
     a.view = v.viewmatrix; a.proj = v.projmatrix; a.campos = v.cam_pos;
+    a.zero_a = nullptr; a.zero_a_words = 0; a.zero_b = nullptr; a.zero_b_words = 0;
 }
 
 
@@ -755,9 +766,12 @@ static bool sh16_fast(const gsr_view& v) {
     return v.sh_dc == nullptr && v.shs != nullptr && v.M == 16 && (reinterpret_cast<uintptr_t>(v.shs) & 15) == 0;
 }
 
-int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s) {
+int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s, void* zero_a, size_t zero_a_bytes,
+                      void* zero_b, size_t zero_b_bytes) {
     PreArgs a;
     fill_pre_args(v, a);
+    a.zero_a = reinterpret_cast<uint32_t*>(zero_a); a.zero_a_words = (long long)(zero_a_bytes / 4);
+    a.zero_b = reinterpret_cast<uint32_t*>(zero_b); a.zero_b_words = (long long)(zero_b_bytes / 4);
     constexpr int kThreads = 128;
     const int blocks = (v.P + kThreads - 1) / kThreads;
     uint32_t* tiles_touched = rect_packing_ok(v.W, v.H) ? nullptr : g.tiles_touched;

@@ -118,15 +118,30 @@ def emulated_exchange_adam(grads, params, exp_avg, exp_avg_sq, spans, beta1, bet
 class PeerExchange:
     """Flat fp32 buffer in symmetric memory + the descriptor gsr_allreduce_sum needs. Collective constructor."""
 
-    def __init__(self, numel: int, device, group=None, multicast=True):
+    def __init__(self, numel: int, device, group=None, multicast=True, agree=None):
+        """agree(ok: bool) -> bool, optional: a collective AND over the ranks, called between the local and the collective
+        stages of the set-up. With it, a rank whose local allocation failed and the healthy ranks all learn so BEFORE
+        anybody enters the rendezvous, and every rank raises together instead of running mismatched collectives
+        (ADVICE r1). Without it a local failure simply raises on that rank."""
         import torch.distributed._symmetric_memory as symm_mem
         L, _ = _gsr()
         group = group if group is not None else dist.group.WORLD
         if numel % 4:
             raise ValueError("peer exchange needs a multiple of 4 elements")
-        self.flat = symm_mem.empty(numel, dtype=torch.float32, device=device)
+        # ---- stage 1: local (no collective): the two symmetric allocations
+        err = None
+        try:
+            self.flat = symm_mem.empty(numel, dtype=torch.float32, device=device)
+            self.signal = symm_mem.empty(L.gsr_comm_signal_bytes() // 4, dtype=torch.int32, device=device)
+        except Exception as e:          # noqa: BLE001
+            err = e
+        if agree is not None:
+            if not agree(err is None):
+                raise RuntimeError(f"symmetric allocation failed on some rank ({err})")
+        elif err is not None:
+            raise err
+        # ---- stage 2: collective on every rank (rendezvous x 2, barrier)
         self.hdl = symm_mem.rendezvous(self.flat, group)
-        self.signal = symm_mem.empty(L.gsr_comm_signal_bytes() // 4, dtype=torch.int32, device=device)
         self.signal.zero_()
         self.sig_hdl = symm_mem.rendezvous(self.signal, group)
         self.flat.zero_()
@@ -314,17 +329,25 @@ class GradBucket:
                       zip(self.params.items(), self.offsets.values())}
 
     def _try_peer(self, numel, mode, group):
-        """Sets the peer-memory exchange up on all ranks or on none (the ranks agree through a MIN all-reduce)."""
+        """Sets the peer-memory exchange up on all ranks or on none. Every rank goes through the same collectives in the
+        same order whatever fails where: agreement (a MIN all-reduce) after the local allocations, the rendezvous only if
+        all of them succeeded, agreement again after it."""
+        def agree(ok: bool) -> bool:
+            t = torch.tensor([1 if ok else 0], device=self.device, dtype=torch.int32)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+            return int(t.item()) == 1
+
         px, err = None, None
         try:
-            px = PeerExchange(numel, self.device, group, multicast={"peer": False, "multimem": True}.get(mode, "auto"))
+            px = PeerExchange(numel, self.device, group, multicast={"peer": False, "multimem": True}.get(mode, "auto"),
+                              agree=agree)
             if mode == "multimem" and not px.has_multicast:
                 raise RuntimeError("no NVSwitch multicast mapping for the bucket")
         except Exception as e:          # noqa: BLE001 - any set-up failure means "not available here"
             px, err = None, e
-        ok = torch.tensor([1 if px is not None else 0], device=self.device, dtype=torch.int32)
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
-        if int(ok.item()) == 1:
+        # a failure in stage 1 was agreed on inside the constructor and raised on every rank alike, so all ranks arrive
+        # here having run the same collectives; this second agreement covers asymmetric failures after the rendezvous
+        if agree(px is not None):
             return px
         if mode != "auto":
             raise RuntimeError(f"GSR_EXCHANGE={mode} requested but peer memory could not be set up: {err}")

@@ -6,3 +6,7 @@ python bench.py --steps 10 --warmup 3 --no-extras --no-cpu-baseline > gpurun_out
 python bench.py --workload c1 --steps 10 --warmup 3 > gpurun_out/bench_c1_ours.json 2> gpurun_out/bench_c1_ours.err
 python bench.py --workload slam --steps 10 --warmup 3 > gpurun_out/bench_slam_ours.json 2> gpurun_out/bench_slam_ours.err
 python bench.py --workload knn --steps 10 --warmup 3 > gpurun_out/bench_knn_ours.json 2> gpurun_out/bench_knn_ours.err
+python tools/diag_host.py c1 ours > gpurun_out/diag_host_c1_ext.txt 2>&1
+GSR_BINDING=ctypes python tools/diag_host.py c1 ours > gpurun_out/diag_host_c1_ctypes.txt 2>&1
+GSR_BINDING=ctypes python bench.py --workload c1 --steps 10 --warmup 3 > gpurun_out/bench_c1_ctypes.json 2> gpurun_out/bench_c1_ctypes.err
+head -1 gpurun_out/diag_host_c1_ext.txt gpurun_out/diag_host_c1_ctypes.txt
