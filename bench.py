@@ -100,6 +100,9 @@ class ClockSampler:
 
     def start(self):
         self.stop_flag.clear()
+        if os.environ.get("GSR_BENCH_NO_SAMPLER"):          # diagnosis only: a line without clocks is not a bench value
+            self.nv, self.proc = None, None
+            return
         if self.nv is not None:
             self.t = threading.Thread(target=self._poll, daemon=True)
             self.t.start()
@@ -438,11 +441,14 @@ def work_model(arm, args):
         "onesweep_depth": ("hbm", 8.0 * P + 8.0 * visible + 3 * 16.0 * visible),
         # instance sort by tile id: 8 B read + 8 B written per pair and pass; the last pass writes no keys
         "onesweep_tile": ("hbm", 16.0 * rp * R - 4.0 * R),
-        # scan + emission in one kernel: order + packed rectangle read, offsets written per visible Gaussian; (tile id,
-        # Gaussian id) written per instance; 4 RED operations per visible Gaussian into the difference array (L2)
-        "scan_emit": ("hbm", 12.0 * visible + 8.0 * R),
-        # one CTA: difference array -> ranges + digit histograms
-        "tile_table": ("hbm", 4.0 * (tiles + 200) + 8.0 * tiles),
+        # chained scan in depth order: id + packed rectangle read, offset + sorted rectangle written per visible Gaussian
+        "scan_offsets": ("hbm", 16.0 * visible),
+        # emission balanced by output: (tile id, Gaussian id) written per instance; offset, id and rectangle read per
+        # visible Gaussian
+        "emit_instances": ("hbm", 12.0 * visible + 8.0 * R),
+        "count_instances": ("hbm", 4.0 * P),
+        # packed rectangles of all P Gaussians read once; difference array -> ranges + digit histograms
+        "tile_table": ("hbm", 4.0 * P + 4.0 * (tiles + 200) + 8.0 * tiles),
         # 13 flop for every (pixel, list entry) pair the reference iterates (power + alpha test);
         # a contributing pair costs 22 flop in the forward and ~80 in the backward
         "blend_forward": ("fp32", 13.0 * (traversed - contributing) + 22.0 * contributing),

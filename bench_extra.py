@@ -133,8 +133,10 @@ def run_small(args, dev, emit, out_fd, ClockSampler, local):
     sampler = ClockSampler(local)
     sampler.start()
     l0 = arm.launches()
+    m0 = torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
     ms, wall = _timed_steps(torch, arm.step, args.steps)
     launches = arm.launches() - l0
+    device_allocs = torch.cuda.memory_stats(dev).get("num_device_alloc", 0) - m0      # cudaMalloc calls of the caching allocator
     kernels = None
     if args.impl == "ours" and not args.no_kernel_timing:
         arm._C.profile_enable(True)
@@ -159,6 +161,7 @@ def run_small(args, dev, emit, out_fd, ClockSampler, local):
                       "l2": "config-defined sizes: c1 (1 MB) and slam (50 MB) fit the 126 MB L2 by definition of the config; "
                             "every view still runs its full kernel chain"},
            "clocks": clocks, "gpu_launches": launches if args.impl == "ours" else None,
+           "cuda_mallocs_in_timed_region": device_allocs,
            "e2e": {"value": round(views / (wall / 1e3), 2), "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                    "note": "host wall clock of the same loop (these configs are host-launch bound); cameras resident"}}
     if args.impl == "reference":

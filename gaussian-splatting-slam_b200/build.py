@@ -34,7 +34,11 @@ def build_torch_binding(verbose=False):
            "-DTORCH_API_INCLUDE_EXTENSION_H", f"-I{ti}/include", f"-I{ti}/include/torch/csrc/api/include",
            f"-I{sysconfig.get_paths()['include']}", "-I/usr/local/cuda/include", src, "-o", TORCH_EXT, f"-L{ti}/lib",
            "-ltorch", "-ltorch_cpu", "-ltorch_cuda", "-lc10", "-lc10_cuda", "-ltorch_python", f"-L{HERE}", "-lgsr",
-           "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{ti}/lib"]
+           "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{ti}/lib",
+           # the SHARED libstdc++ torch itself runs on. (A compiler whose search path only finds libstdc++.a links a
+           # private copy of the iostream / locale code into the module; two copies in one process disagree about the
+           # locale facet ids and the first formatted integer in an error message crashes.)
+           "-nostdlib++", "-l:libstdc++.so.6"]
     if verbose:
         print(" ".join(cmd), file=sys.stderr)
     subprocess.check_call(cmd)

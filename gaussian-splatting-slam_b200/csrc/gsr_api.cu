@@ -358,7 +358,8 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
     if (!cold) {
         bp = binning_alloc(binning_ctx, blob_size_binning((size_t)cap, (size_t)v.P, v.W, v.H));
         if (!bp) return GSR_E_ALLOC;
-        BinningState b0 = BinningState::from(bp, (size_t)cap, (size_t)v.P, v.W, v.H);
+        char* bq = bp;                                                // from() advances the pointer it is given
+        BinningState b0 = BinningState::from(bq, (size_t)cap, (size_t)v.P, v.W, v.H);
         e = launch_preprocess(v, g, radii, s, za, zan, b0.zero_begin, (size_t)(b0.zero_end - b0.zero_begin));
         if (e) return e;
         binning_zeroed = true;
@@ -401,7 +402,8 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
             bp = binning_alloc(binning_ctx, blob_size_binning((size_t)cap, (size_t)v.P, v.W, v.H));
             if (!bp) return GSR_E_ALLOC;
         }
-        BinningState b = BinningState::from(bp, (size_t)cap, (size_t)v.P, v.W, v.H);
+        char* bq = bp;
+        BinningState b = BinningState::from(bq, (size_t)cap, (size_t)v.P, v.W, v.H);
         bp = nullptr;                                                 // a repeat allocates a new blob
         uint32_t* total_dev = nullptr;
         if (!table_done) {

@@ -146,3 +146,16 @@ def test_product_path_never_imports_the_oracle():
                 if re.search(r"^\s*(from|import)\s+oracle\b|gsr_oracle|libgsr_oracle|ref_dgr_C|ref_cuda", txt, flags=re.M):
                     bad.append(f)
     assert not bad, f"product files reference the checker: {bad}"
+
+
+def test_torch_binding_shares_the_process_libstdcxx():
+    """_gsr_torch.so must use the shared libstdc++ torch runs on: a private, statically linked copy of the iostream code
+    (what a compiler that only finds libstdc++.a produces) crashes in the first error message that formats an integer."""
+    import shutil
+    import subprocess
+    so = os.path.join(ROOT, "gaussian-splatting-slam_b200", "_gsr_torch.so")
+    if not os.path.exists(so) or not shutil.which("nm"):
+        pytest.skip("_gsr_torch.so not built / nm missing")
+    syms = subprocess.run(["nm", "-D", "--defined-only", so], capture_output=True, text=True, check=True).stdout
+    private = [ln for ln in syms.splitlines() if "_ZNSo" in ln or "_ZNSt6locale" in ln]
+    assert not private, private[:5]
