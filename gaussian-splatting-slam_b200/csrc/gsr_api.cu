@@ -167,6 +167,9 @@ const char* gsr_error_string(int code) {
         case GSR_E_BADARG: return "gsr: bad argument";
         case GSR_E_TOOLARGE: return "gsr: too large (num_rendered >= 2^30 - 1, or more than 2^20 tiles)";
         case GSR_E_ALLOC: return "gsr: scratch allocation callback returned NULL";
+        case GSR_E_STATIC_LIMIT:
+            return "gsr: input larger than the fixed scratch of a no-allocation entry point (gsr_dist2_noalloc: at most "
+                   "131072 points; use gsr_dist2 with a caller-supplied buffer)";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "gsr: unknown error";
     }
 }
@@ -492,6 +495,11 @@ int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const
 int gsr_dist2(int P, const float* points_xyz, float* mean_d2, char* temp, void* stream) {
     if (P < 0 || (P > 0 && (!points_xyz || !mean_d2 || !temp))) return GSR_E_BADARG;
     return launch_dist2(P, points_xyz, mean_d2, temp, (cudaStream_t)stream);
+}
+
+int gsr_dist2_noalloc(int P, const float* points_xyz, float* mean_d2, void* stream) {
+    if (P < 0 || (P > 0 && (!points_xyz || !mean_d2))) return GSR_E_BADARG;
+    return launch_dist2_noalloc(P, points_xyz, mean_d2, (cudaStream_t)stream);
 }
 
 // Parity helper (not on the hot path): reconstruct the reference's sorted 64-bit keys

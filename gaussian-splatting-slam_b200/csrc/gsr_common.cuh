@@ -281,5 +281,6 @@ int launch_exp_check(unsigned long long* mismatches_dev, cudaStream_t s);
 int launch_fp32_peak(int iters, float* out, int* sms_out, cudaStream_t s);
 int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s);
 size_t dist2_temp_bytes(int P);
+int launch_dist2_noalloc(int P, const float* pts, float* out, cudaStream_t s);   // scratch in a static device array
 
 }  // namespace gsr

@@ -14,6 +14,7 @@
 //     memory, and every thread scans only those whose box distance beats its current third-best.
 // The result is the exact 3-NN mean, so it equals the reference up to fp32 rounding of d^2.
 #include "gsr_common.cuh"
+#include <mutex>
 #include <cfloat>
 
 namespace gsr {
@@ -307,6 +308,40 @@ int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s
     GSR_LAUNCH("knn_boxes", false, s, (box_from_sub_kernel<<<(nb + 255) / 256, 256, 0, s>>>(nb, nsub, t.sub, t.boxes)));
     GSR_LAUNCH("knn_search", false, s, (knn_kernel<<<blocks, 256, 0, s>>>(P, t.sorted, t.boxes, nb, t.sub, nsub, out)));
     return 0;
+}
+
+// ------------------------------------------------------------------ no-allocation variant (gsr_dist2_noalloc)
+// Same kernels as launch_dist2, with the scratch in a file-scope device array instead of a caller-supplied buffer: for
+// callers that cannot obtain device memory at the call (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc). Every GPU that loads the library holds the array (4.5 MiB) until exit. All calls on a device SHARE it:
+// calls that overlap on the GPU (different streams) race. The chain clears what it needs at the start of every call
+// (bounding box words, the sort's tables), so the previous call's contents do not matter.
+constexpr size_t kNoAllocScratchBytes = 4608u * 1024u;       // >= dist2_temp_bytes(GSR_DIST2_NOALLOC_MAX_POINTS) = 4400256
+static __device__ __align__(256) unsigned char g_dist2_static_scratch[kNoAllocScratchBytes];
+
+int launch_dist2_noalloc(int P, const float* pts, float* out, cudaStream_t s) {
+    if (P <= 0) return 0;
+    if (P > GSR_DIST2_NOALLOC_MAX_POINTS || dist2_temp_bytes(P) > kNoAllocScratchBytes) return GSR_E_STATIC_LIMIT;
+    int dev = 0;
+    { const int e = current_device(&dev); if (e) return e; }
+    if (dev < 0 || dev >= kMaxDevices) return GSR_E_BADARG;
+    // In host code the array's name is only a stand-in; the device address comes from cudaGetSymbolAddress, once per
+    // device, with that device current (it is: current_device() just reported it).
+    static std::mutex mu;
+    static char* addr[kMaxDevices] = {};
+    char* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!addr[dev]) {
+            void* p = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress(&p, g_dist2_static_scratch);
+            if (e != cudaSuccess) return (int)e;
+            if (!p) return GSR_E_BADARG;
+            addr[dev] = static_cast<char*>(p);
+        }
+        scratch = addr[dev];
+    }
+    return launch_dist2(P, pts, out, scratch, s);
 }
 
 }  // namespace gsr

@@ -73,6 +73,8 @@ def lib():
         L.gsr_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.gsr_dist2.restype = C.c_int
         L.gsr_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.gsr_dist2_noalloc.restype = C.c_int
+        L.gsr_dist2_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.gsr_debug_blend_stats.restype = C.c_int
         L.gsr_debug_blend_stats.argtypes = [C.POINTER(_View), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.gsr_debug_exp_mismatches.restype = C.c_int
