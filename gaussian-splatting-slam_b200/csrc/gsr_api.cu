@@ -691,6 +691,7 @@ int gsr_debug_blend_stats(const gsr_view* view, int R, const char* geom, const c
 
 int gsr_debug_set_exact_cull(int on) { return set_exact_cull(on); }
 int gsr_debug_set_blend_variant(int v) { return set_blend_variant(v); }
+int gsr_debug_set_comm_variant(int v) { return set_comm_variant(v); }
 
 int gsr_debug_fp32_peak(int iters, float* out, int* sms_out, void* stream) {
     if (iters <= 0 || !out) return GSR_E_BADARG;

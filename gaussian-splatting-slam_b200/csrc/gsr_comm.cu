@@ -17,12 +17,18 @@
 // Bound: NVLink -- per rank (world-1)/world of the bucket leaves and enters through the switch.
 #include "gsr_common.cuh"
 #include <cuda/atomic>
+#include <algorithm>
 
 namespace gsr {
 
 constexpr int kCommThreads = 512;
 constexpr int kCommUnroll = 4;          // 16-byte requests in flight per thread and peer (peer variant)
-constexpr int kCommUnrollMc = 8;        // multicast variant: one request covers all peers, registers allow more in flight
+constexpr int kCommUnrollMc = 4;        // multicast variant. Measured at 8 ranks (tools/comm_sweep.py, profiles/r02_comm_sweep_n8.json):
+                                        // 4 requests in flight on sms/2 CTAs 1.63 ms, 8 on 2*sms CTAs 1.70 ms, 16: 1.71-1.81 ms.
+                                        // One stream alone (ld_reduce only / multimem.st only) moves the 708 MB in 1.06 ms
+                                        // (665 GB/s per direction); together they reach 490 GB/s whether they alternate in
+                                        // a thread or run in separate producer / consumer CTAs (variant 3): the fabric, not
+                                        // the SMs' issue order, is what they share.
 
 struct CommArgs {
     float4* buf[GSR_COMM_MAX_PEERS];
@@ -144,6 +150,107 @@ template <bool MULTICAST, int WORLD>
 __global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_kernel(const __grid_constant__ CommArgs a) {
     allreduce_sum_body<MULTICAST, WORLD>(a, (int)blockIdx.x, (int)gridDim.x);
 }
+// ---- multicast variants (selected with GSR_COMM_VARIANT, measured with tools/comm_sweep.py) ---------------------------
+// SPLIT: the rank's CTAs are pairs (producer c, consumer c + n/2) that share the c-th share of the slice. The producer
+// streams multimem.ld_reduce and parks the sums in the rank's OWN replica (plain stores: they stay in L2); the consumer
+// follows chunk by chunk behind a counter and streams multimem.st. Each link direction then carries one uninterrupted
+// request stream (reduce: data leaves every GPU, broadcast: data enters every GPU) instead of alternating bursts.
+constexpr int kSplitUnroll = 8;                                   // 512 threads x 8 x 16 B = 64 KB per chunk
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ uint32_t g_split_ready[GSR_COMM_MAX_CTAS];           // chunks parked per pair; zero between launches
+__global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_split_kernel(const __grid_constant__ CommArgs a) {
+    uint32_t* ready = g_split_ready;
+    const int cta = (int)blockIdx.x, half = (int)gridDim.x / 2;
+    twin_barrier(a, cta);
+    const bool producer = cta < half;
+    const int pair = producer ? cta : cta - half;
+    float4* own = a.buf[a.rank];
+    const long long chunk = (long long)kCommThreads * kSplitUnroll;
+    uint32_t k = 0;
+    for (long long base = a.lo + (long long)pair * chunk; base < a.hi; base += (long long)half * chunk, k++) {
+        const long long i0 = base + threadIdx.x;
+        if (producer) {
+            float4 v[kSplitUnroll];
+#pragma unroll
+            for (int u = 0; u < kSplitUnroll; u++)
+                if (i0 + u * kCommThreads < a.hi) v[u] = mc_ld_reduce(a.mc + i0 + u * kCommThreads);
+#pragma unroll
+            for (int u = 0; u < kSplitUnroll; u++)
+                if (i0 + u * kCommThreads < a.hi) own[i0 + u * kCommThreads] = v[u];
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0) atomicAdd(ready + pair, 1u);
+        } else {
+            if (threadIdx.x == 0) {
+                uint32_t spins = 0;
+                while (ld_acquire_gpu(ready + pair) <= k) {
+                    if (++spins > 64u) __nanosleep(64);
+                    if (spins > kSpinLimit) sig_fail(a.sig[a.rank]);
+                }
+            }
+            __syncthreads();
+            float4 v[kSplitUnroll];
+#pragma unroll
+            for (int u = 0; u < kSplitUnroll; u++)
+                if (i0 + u * kCommThreads < a.hi) v[u] = __ldcg(own + i0 + u * kCommThreads);
+#pragma unroll
+            for (int u = 0; u < kSplitUnroll; u++)
+                if (i0 + u * kCommThreads < a.hi) mc_st(a.mc + i0 + u * kCommThreads, v[u]);
+        }
+    }
+    if (!producer) {                                               // the producer wrote its last chunk: rearm the counter
+        __syncthreads();
+        if (threadIdx.x == 0) ready[pair] = 0u;
+    }
+    twin_barrier(a, cta);
+}
+// PROBES (not an all-reduce: they measure what one request stream alone reaches; the bucket's contents are garbage
+// afterwards). mode 1: multimem.ld_reduce only, mode 2: multimem.st only.
+template <int MODE, int U>
+__global__ void __launch_bounds__(kCommThreads, 2) comm_probe_kernel(const __grid_constant__ CommArgs a) {
+    const int cta = (int)blockIdx.x;
+    twin_barrier(a, cta);
+    const long long stride = (long long)gridDim.x * kCommThreads;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (long long i0 = a.lo + (long long)cta * kCommThreads + threadIdx.x; i0 < a.hi; i0 += stride * U) {
+        if (MODE == 1) {
+            float4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; u++)
+                if (i0 + u * stride < a.hi) v[u] = mc_ld_reduce(a.mc + i0 + u * stride);
+#pragma unroll
+            for (int u = 0; u < U; u++)
+                if (i0 + u * stride < a.hi) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+        } else {
+#pragma unroll
+            for (int u = 0; u < U; u++)
+                if (i0 + u * stride < a.hi) mc_st(a.mc + i0 + u * stride, make_float4((float)u, 1.f, 2.f, 3.f));
+        }
+    }
+    if (MODE == 1 && acc.x + acc.y + acc.z + acc.w == 123.456f) a.buf[a.rank][a.lo] = acc;      // keeps the loads alive
+    twin_barrier(a, cta);
+}
+template <int U>
+__global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_mc_unroll_kernel(const __grid_constant__ CommArgs a) {
+    const int cta = (int)blockIdx.x;
+    twin_barrier(a, cta);
+    const long long stride = (long long)gridDim.x * kCommThreads;
+    for (long long i0 = a.lo + (long long)cta * kCommThreads + threadIdx.x; i0 < a.hi; i0 += stride * U) {
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (i0 + u * stride < a.hi) v[u] = mc_ld_reduce(a.mc + i0 + u * stride);
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (i0 + u * stride < a.hi) mc_st(a.mc + i0 + u * stride, v[u]);
+    }
+    twin_barrier(a, cta);
+}
+
 // Emulated ranks on ONE device (tests without a second GPU): a single cooperative launch whose blockIdx.y is the rank.
 // Separate launches that wait for one another are not guaranteed to run at the same time; one cooperative grid is.
 __global__ void __launch_bounds__(kCommThreads, 2) allreduce_sum_emulated_kernel(const CommArgs* __restrict__ all) {
@@ -240,6 +347,9 @@ __global__ void __launch_bounds__(kCommThreads, 2) exchange_adam_emulated_kernel
     exchange_adam_body<false, 0>(all[blockIdx.y], (int)blockIdx.x, (int)gridDim.x);
 }
 
+static int g_comm_variant = 0;           // gsr_debug_set_comm_variant: experiments of the multicast path, 0 = product kernel
+int set_comm_variant(int v) { g_comm_variant = v; return 0; }
+
 void comm_slice(long long n16, int rank, int world, long long* lo, long long* hi) {
     const long long per = (n16 + world - 1) / world;
     const long long l = per * rank < n16 ? per * rank : n16;
@@ -259,13 +369,15 @@ static void fill_comm_args(const gsr_peer_group& g, long long numel, CommArgs& a
     comm_slice(numel / 4, g.rank, g.world, &a.lo, &a.hi);
 }
 // the grid must be the same on every rank (CTAs meet their twins): derive it from the largest slice only
-static int comm_grid(long long numel, int world, int max_ctas, int per_cta_units, unsigned* grid) {
+static int comm_grid(long long numel, int world, int max_ctas, int per_cta_units, unsigned* grid, bool multicast = false) {
     int sms = 0;
     { const int e = sm_count(&sms); if (e) return e; }
     const long long n16 = numel / 4;
     const long long per = (n16 + world - 1) / world;
     long long ctas = (per + (long long)kCommThreads * per_cta_units - 1) / ((long long)kCommThreads * per_cta_units);
-    long long cap = max_ctas > 0 ? max_ctas : 2 * sms;
+    // multicast requests are served by the switch: half an SM count of CTAs already saturates the links (and leaves the
+    // other SMs to whatever else the stream's neighbours run); the peer path needs every SM's load/store slots
+    long long cap = max_ctas > 0 ? max_ctas : (multicast ? std::max(1, sms / 2) : 2 * sms);
     if (cap > GSR_COMM_MAX_CTAS) cap = GSR_COMM_MAX_CTAS;
     if (ctas > cap) ctas = cap;
     if (ctas < 1) ctas = 1;
@@ -277,7 +389,23 @@ int launch_allreduce_sum(const gsr_peer_group& g, long long numel, int max_ctas,
     CommArgs a;
     fill_comm_args(g, numel, a);
     unsigned grid = 1;
-    { const int e = comm_grid(numel, g.world, max_ctas, kCommUnroll, &grid); if (e) return e; }
+    { const int e = comm_grid(numel, g.world, max_ctas, kCommUnroll, &grid, a.mc != nullptr); if (e) return e; }
+    const int variant = g_comm_variant;
+    if (a.mc != nullptr && variant != 0) {
+        // experiments (tools/comm_sweep.py): 1 / 2 = probes (NOT an all-reduce), 3 = producer/consumer split,
+        // 4 / 16 = unroll of the fused loop
+        switch (variant) {
+            case 1: GSR_LAUNCH("comm_probe_ld", false, s, (comm_probe_kernel<1, 8><<<grid, kCommThreads, 0, s>>>(a))); return 0;
+            case 2: GSR_LAUNCH("comm_probe_st", false, s, (comm_probe_kernel<2, 8><<<grid, kCommThreads, 0, s>>>(a))); return 0;
+            case 3:
+                if (grid < 2) break;
+                GSR_LAUNCH("allreduce_sum_split", false, s, (allreduce_sum_split_kernel<<<grid & ~1u, kCommThreads, 0, s>>>(a)));
+                return 0;
+            case 4: GSR_LAUNCH("allreduce_sum_mc_u4", false, s, (allreduce_sum_mc_unroll_kernel<4><<<grid, kCommThreads, 0, s>>>(a))); return 0;
+            case 16: GSR_LAUNCH("allreduce_sum_mc_u16", false, s, (allreduce_sum_mc_unroll_kernel<16><<<grid, kCommThreads, 0, s>>>(a))); return 0;
+            default: break;
+        }
+    }
     if (a.mc != nullptr)
         GSR_LAUNCH("allreduce_sum_multimem", false, s, (allreduce_sum_kernel<true, 0><<<grid, kCommThreads, 0, s>>>(a)));
     else if (g.world == 2)

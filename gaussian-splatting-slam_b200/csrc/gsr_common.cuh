@@ -263,6 +263,7 @@ int launch_densify_stats(int P, const float* dL_dmean2D, const uint8_t* update_f
                          float* denom, float* max_radii2D, cudaStream_t s);
 int set_exact_cull(int on);
 int set_blend_variant(int v);
+int set_comm_variant(int v);
 int launch_cull_stats(const gsr_view& v, const GeomState& g, const uint32_t* point_list, const ImageState& img,
                       unsigned long long* out, cudaStream_t s);
 int launch_adam(const gsr_adam_group* groups, int n, double b1, double b2, double eps, const uint8_t* visible, cudaStream_t s);

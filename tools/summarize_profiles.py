@@ -15,7 +15,8 @@ out_dir = os.path.join(ROOT, "profiles")
 def short(name):
     m = re.search(r"(\w+)_kernel", name)
     if m:
-        return m.group(1)
+        k = m.group(1)
+        return {"blend_backward_streams": "blend_backward", "blend_forward_streams": "blend_forward"}.get(k, k)
     return re.sub(r"\(.*", "", name).split("::")[-1][:40]
 
 # ---- launch list: share of the captured window per kernel
@@ -29,8 +30,8 @@ total_ms = sum(v[1] for v in tot.values())
 share = {k: {"launches": v[0], "ms": round(v[1], 4), "share": round(v[1] / total_ms, 4)} for k, v in
          sorted(tot.items(), key=lambda kv: -kv[1][1])}
 shutil.copy(launches, os.path.join(out_dir, f"{tag}_ncu_launches_bench.csv"))
-json.dump({"command": "ncu --metrics gpu__time_duration.sum --clock-control none -s 700 -c 300 python bench.py --steps 2 --warmup 3 "
-                      "--no-cpu-baseline --no-e2e", "captured_launches": len(rows), "total_ms": round(total_ms, 4),
+json.dump({"command": "ncu --metrics gpu__time_duration.sum --clock-control none -c 800 python bench.py --steps 2 --warmup 3 --no-extras "
+                      "--no-cpu-baseline --no-e2e --no-kernel-timing (tools/gpu_ncu_list.sh)", "captured_launches": len(rows), "total_ms": round(total_ms, 4),
            "per_kernel": share}, open(os.path.join(out_dir, f"{tag}_ncu_launch_shares.json"), "w"), indent=1)
 
 # ---- full capture
@@ -68,14 +69,17 @@ for row in data:
                 pass
     e["stalls_per_issue"] = dict(sorted(stalls.items(), key=lambda kv: -kv[1])[:5])
     e["grid"] = row[col["Grid Size"]] if "Grid Size" in col else None
+    if k == "onesweep":                      # same template for both sorts: the depth sort has as many CTAs as P needs
+        seen_onesweep = len(summary.get("onesweep_depth", [])) + len(summary.get("onesweep_tile", []))
+        k = "onesweep_depth" if seen_onesweep < 4 else "onesweep_tile"
     summary.setdefault(k, []).append(e)
     traffic[k].append(e.get("dram_read_bytes", 0) + e.get("dram_write_bytes", 0))
-json.dump({"command": "ncu --set full --clock-control none --import-source on python tools/prof_view.py 2  (one 3M-Gaussian 1080p view)",
+json.dump({"command": "ncu --set full --clock-control none --import-source on -k regex:... --launch-skip 350 -c 14 python bench.py --steps 1 "
+                      "--warmup 3 ... (tools/gpu_ncu_full.sh: the 14 launches of one 3M-Gaussian 1080p view of the timed step)",
            "kernels": summary}, open(os.path.join(out_dir, f"{tag}_ncu_full_summary.json"), "w"), indent=1)
 # bench.py names (per-launch DRAM bytes, mean over the captured launches of that kernel)
-name_map = {"blend_forward": "blend_forward", "blend_backward": "blend_backward", "preprocess_fwd": "preprocess_fwd",
-            "preprocess_bwd": "preprocess_bwd", "emit_instances": "emit_instances", "onesweep": "onesweep_pass",
-            "radix_hist": "radix_hist", "tile_ranges": "tile_ranges"}
+name_map = {k: k for k in ("blend_forward", "blend_backward", "preprocess_fwd", "preprocess_bwd", "emit_instances",
+                           "onesweep_depth", "onesweep_tile", "radix_hist", "tile_table", "scan_offsets")}
 tr = {name_map[k]: round(sum(v) / len(v)) for k, v in traffic.items() if k in name_map}
 json.dump(tr, open(os.path.join(out_dir, "ncu_traffic.json"), "w"), indent=1)
 print(json.dumps(share, indent=1)); print(json.dumps(tr))
