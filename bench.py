@@ -223,6 +223,7 @@ class OursArm:
         self.params = device_params(sc, dev)
         self.means2D = torch.zeros_like(self.params["means3D"], requires_grad=True)    # the caller's grad sink
         self.bucket = GradBucket(self.params)
+        self.sinks_first = self.bucket.views_first
         self.bg = torch.zeros(3, device=dev)
         self.cams_host = cams
         self.cams_dev = [(c.viewmatrix.to(dev), c.projmatrix.to(dev), c.campos.to(dev)) for c in cams]
@@ -258,11 +259,17 @@ class OursArm:
                              scale_modifier=1.0, viewmatrix=view, projmatrix=proj, sh_degree=self.deg, campos=campos,
                              prefiltered=False, debug=False, antialiasing=False)
 
-    def _view(self, st, dpix):
+    def _sinks(self, first):
+        """grad_sinks of a view: the first view of a step overwrites the bucket (no bucket.zero()), the others add."""
+        if self.args.no_grad_sinks:
+            return None
+        return self.sinks_first if first else self.bucket.views
+
+    def _view(self, st, dpix, first=False):
         p = self.params
         color, radii, _invd = self.Rasterizer(st)(means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"],
                                                   shs=p["shs"], scales=p["scales"], rotations=p["rotations"],
-                                                  grad_sinks=None if self.args.no_grad_sinks else self.bucket.views)
+                                                  grad_sinks=self._sinks(first))
         if self.train:
             self.loss_fn(color, self.gt, 0.2).backward()          # train.py:114-122 (lambda_dssim = 0.2)
         else:
@@ -271,11 +278,12 @@ class OursArm:
         return color
 
     def step(self):
-        self.bucket.zero()
+        if self.args.no_grad_sinks:
+            self.bucket.zero()                    # autograd adds into .grad: the bucket has to start at zero
         self.bucket.attach()
         self.means2D.grad = None
-        for cam, (v, pj, cp) in zip(self.cams_host, self.cams_dev):
-            self._view(self._settings(cam, v, pj, cp), self.dpix)
+        for i, (cam, (v, pj, cp)) in enumerate(zip(self.cams_host, self.cams_dev)):
+            self._view(self._settings(cam, v, pj, cp), self.dpix, first=(i == 0))
         if self.train and self.fused_opt:
             self.opt.step()                       # gsr_exchange_adam_step: the exchange and the optimiser in one launch
         else:
@@ -299,7 +307,8 @@ class OursArm:
                 down=[torch.cuda.Event() for _ in range(n)])
         e = self._e2e
         main = torch.cuda.current_stream(self.dev)
-        self.bucket.zero()
+        if self.args.no_grad_sinks:
+            self.bucket.zero()
         self.bucket.attach()
         self.means2D.grad = None
         n_views = len(self.cams_host)
@@ -323,7 +332,7 @@ class OursArm:
             p = self.params
             color, radii, _invd = self.Rasterizer(self._settings(cam, b[0:16].view(4, 4), b[16:32].view(4, 4), b[32:35]))(
                 means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"], shs=p["shs"], scales=p["scales"],
-                rotations=p["rotations"], grad_sinks=None if self.args.no_grad_sinks else self.bucket.views)
+                rotations=p["rotations"], grad_sinks=self._sinks(i == 0))
             rendered = torch.cuda.Event()
             rendered.record(main)
             with torch.cuda.stream(e["d2h"]):                     # the image goes home while the backward runs
@@ -441,11 +450,14 @@ def work_model(arm, args):
         "onesweep_depth": ("hbm", 8.0 * P + 8.0 * visible + 3 * 16.0 * visible),
         # instance sort by tile id: 8 B read + 8 B written per pair and pass; the last pass writes no keys
         "onesweep_tile": ("hbm", 16.0 * rp * R - 4.0 * R),
-        # chained scan in depth order: id + packed rectangle read, offset + sorted rectangle written per visible Gaussian
-        "scan_offsets": ("hbm", 16.0 * visible),
+        # pass 2 of the two-launch scan (or the chained one-launch scan of small clouds): parked rectangle read, offset
+        # written per visible Gaussian
+        "scan_offsets": ("hbm", 8.0 * visible),
         # emission balanced by output: (tile id, Gaussian id) written per instance; offset, id and rectangle read per
         # visible Gaussian
         "emit_instances": ("hbm", 12.0 * visible + 8.0 * R),
+        # two-launch scan, pass 1: id + gathered packed rectangle read, rectangle parked in depth order
+        "scan_tile_sums": ("hbm", 12.0 * visible),
         "count_instances": ("hbm", 4.0 * P),
         # packed rectangles of all P Gaussians read once; difference array -> ranges + digit histograms
         "tile_table": ("hbm", 4.0 * P + 4.0 * (tiles + 200) + 8.0 * tiles),

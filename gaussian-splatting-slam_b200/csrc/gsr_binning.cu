@@ -166,6 +166,132 @@ __global__ void __launch_bounds__(kScanThreads) scan_offsets_kernel(const uint32
     }
 }
 
+// The same scan in two launches, for clouds of more than kChainedMaxTiles scan tiles: the chained kernel above is bound by
+// the latency of its look-back chain (ncu at C3: 42 us at 7 % issue activity, barrier + long-scoreboard stalls), two
+// dependent launches without any waiting inside are shorter. Pass 1: every tile gathers its counts through `order`, parks
+// the rectangles in depth order and publishes its sum. Pass 2: every tile adds up the sums in front of it (all threads,
+// 64-bit, saturating as above), scans its own counts -- now a dense read of the parked rectangles -- and writes the same
+// outputs as the chained kernel: offsets, the tiles' inclusive prefixes in status[0..m), the total, the host's copy.
+constexpr int kChainedMaxTiles = 16;
+template <bool PACKED>
+__global__ void __launch_bounds__(kScanThreads) scan_tile_sums_kernel(const uint32_t* __restrict__ n_dev,
+                                                                       const uint32_t* __restrict__ order,
+                                                                       const uint32_t* __restrict__ counts,
+                                                                       uint32_t* __restrict__ sums,
+                                                                       uint32_t* __restrict__ rect_sorted) {
+    __shared__ uint32_t warp_sums[kScanThreads / 32];
+    const int tile = (int)blockIdx.x;
+    const int n = (int)__ldg(n_dev);
+    if (tile * GSR_SCAN_TILE >= n) return;
+    const int base = tile * GSR_SCAN_TILE + threadIdx.x * kScanItems;
+    uint32_t g[kScanItems], v = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) g[i] = 0u;
+    if (base + kScanItems <= n) {
+#pragma unroll
+        for (int q = 0; q < kScanItems / 4; q++) {
+            const uint4 o4 = __ldg(reinterpret_cast<const uint4*>(order + base) + q);
+            g[4 * q] = o4.x; g[4 * q + 1] = o4.y; g[4 * q + 2] = o4.z; g[4 * q + 3] = o4.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < kScanItems; i++)
+            if (base + i < n) g[i] = __ldg(order + base + i);
+    }
+    uint32_t c[kScanItems];
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) c[i] = (base + i < n) ? __ldg(counts + g[i]) : 0u;
+    if (PACKED) {
+        if (base + kScanItems <= n) {
+#pragma unroll
+            for (int q = 0; q < kScanItems / 4; q++)
+                reinterpret_cast<uint4*>(rect_sorted + base)[q] = make_uint4(c[4 * q], c[4 * q + 1], c[4 * q + 2], c[4 * q + 3]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < kScanItems; i++)
+                if (base + i < n) rect_sorted[base + i] = c[i];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) v += PACKED ? ((c[i] >> 16) & 255u) * (c[i] >> 24) : c[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tot = 0;
+#pragma unroll
+        for (int k = 0; k < kScanThreads / 32; k++) tot += warp_sums[k];
+        sums[tile] = tot;                                  // <= 2048 * 255 * 255: fits
+    }
+}
+
+template <bool PACKED>
+__global__ void __launch_bounds__(kScanThreads) scan_apply_sums_kernel(const uint32_t* __restrict__ n_dev,
+                                                                        const uint32_t* __restrict__ order,
+                                                                        const uint32_t* __restrict__ counts,
+                                                                        const uint32_t* __restrict__ sums,
+                                                                        const uint32_t* __restrict__ rect_sorted, int m_slots,
+                                                                        uint32_t* __restrict__ status,
+                                                                        uint32_t* __restrict__ point_offsets,
+                                                                        uint32_t* __restrict__ host_total) {
+    __shared__ uint32_t warp_sums[kScanThreads / 32];
+    __shared__ unsigned long long s_part[kScanThreads / 32];
+    const int tile = (int)blockIdx.x;
+    const int n = (int)__ldg(n_dev);
+    const int m = (n + GSR_SCAN_TILE - 1) / GSR_SCAN_TILE;
+    if (tile >= m) {
+        if (m == 0 && tile == 0 && threadIdx.x == 0 && host_total != nullptr) { *host_total = 0u; __threadfence_system(); }
+        return;
+    }
+    unsigned long long part = 0;
+    for (int i = threadIdx.x; i < tile; i += kScanThreads) part += __ldg(sums + i);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = part;
+    const int base = tile * GSR_SCAN_TILE + threadIdx.x * kScanItems;
+    uint32_t c[kScanItems], v = 0;
+    if (PACKED) {
+        if (base + kScanItems <= n) {
+#pragma unroll
+            for (int q = 0; q < kScanItems / 4; q++) {
+                const uint4 r4 = __ldg(reinterpret_cast<const uint4*>(rect_sorted + base) + q);
+                c[4 * q] = r4.x; c[4 * q + 1] = r4.y; c[4 * q + 2] = r4.z; c[4 * q + 3] = r4.w;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < kScanItems; i++) c[i] = (base + i < n) ? __ldg(rect_sorted + base + i) : 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < kScanItems; i++) c[i] = ((c[i] >> 16) & 255u) * (c[i] >> 24);
+    } else {
+#pragma unroll
+        for (int i = 0; i < kScanItems; i++) c[i] = (base + i < n) ? __ldg(counts + __ldg(order + base + i)) : 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) v += c[i];
+    uint32_t total;
+    const uint32_t ex = block_exclusive_scan(v, warp_sums, total);          // syncs: s_part is visible behind it
+    unsigned long long prefix = 0;
+#pragma unroll
+    for (int k = 0; k < kScanThreads / 32; k++) prefix += s_part[k];
+    if (threadIdx.x == 0) {
+        const unsigned long long incl_sum = prefix + total;
+        const uint32_t sat = incl_sum >= kScanVal ? kScanVal : (uint32_t)incl_sum;
+        status[tile] = kScanIncl | sat;
+        if (tile == m - 1) {
+            status[m_slots] = sat;
+            if (host_total != nullptr) { *host_total = sat; __threadfence_system(); }
+        }
+    }
+    uint32_t run = ex + (prefix >= kScanVal ? kScanVal : (uint32_t)prefix);
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) {
+        run += c[i];
+        if (base + i < n) point_offsets[base + i] = run;
+    }
+}
+
 // Replaces duplicateWithKeys (rasterizer_impl.cu:70-111), balanced by OUTPUT: a CTA writes 4096 consecutive instance
 // slots, whatever number of Gaussians they belong to. (Emitting per Gaussian -- the reference's mapping, one thread per
 // Gaussian -- leaves the near Gaussians, which cover hundreds of tiles each and come first in depth order, to a few
@@ -536,6 +662,8 @@ int launch_tile_table(const gsr_view& v, GeomState& g, const int* radii, Binning
     return 0;
 }
 
+static int g_scan_two_pass = [] { const char* e = getenv("GSR_SCAN_TWO_PASS"); return e ? atoi(e) : 1; }();   // A/B switch
+
 int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningState& b, ImageState& img, uint32_t cap,
                    uint32_t** total_dev, uint32_t* host_total, cudaStream_t s) {
     (void)img;
@@ -555,6 +683,14 @@ int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningSta
         if (rect_packing_ok(v.W, v.H)) {
             const size_t smem = sizeof(uint32_t) * 3 * kEmitMax;
             { const int e = ensure_dynamic_smem(emit_instances_kernel<true>, (int)smem, once_ep); if (e) return e; }
+            if (m > kChainedMaxTiles && g_scan_two_pass) {
+                uint32_t* sums = b.scan_sums + m + 8;
+                GSR_LAUNCH("scan_tile_sums", v.debug, s,
+                           (scan_tile_sums_kernel<true><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.rect_packed, sums, g.rect_sorted)));
+                GSR_LAUNCH("scan_offsets", v.debug, s,
+                           (scan_apply_sums_kernel<true><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.rect_packed, sums, g.rect_sorted,
+                                                                                   m, b.scan_sums, g.point_offsets, host_total)));
+            } else
             GSR_LAUNCH("scan_offsets", v.debug, s,
                        (scan_offsets_kernel<true><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.rect_packed, m, b.scan_sums,
                                                                             g.point_offsets, g.rect_sorted, host_total)));
@@ -564,6 +700,14 @@ int launch_binning(const gsr_view& v, GeomState& g, const int* radii, BinningSta
         } else {
             const size_t smem = sizeof(uint32_t) * 4 * kEmitMax;
             { const int e = ensure_dynamic_smem(emit_instances_kernel<false>, (int)smem, once_eu); if (e) return e; }
+            if (m > kChainedMaxTiles && g_scan_two_pass) {
+                uint32_t* sums = b.scan_sums + m + 8;
+                GSR_LAUNCH("scan_tile_sums", v.debug, s,
+                           (scan_tile_sums_kernel<false><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.tiles_touched, sums, nullptr)));
+                GSR_LAUNCH("scan_offsets", v.debug, s,
+                           (scan_apply_sums_kernel<false><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.tiles_touched, sums, nullptr,
+                                                                                    m, b.scan_sums, g.point_offsets, host_total)));
+            } else
             GSR_LAUNCH("scan_offsets", v.debug, s,
                        (scan_offsets_kernel<false><<<m, kScanThreads, 0, s>>>(g.n_visible, g.order, g.tiles_touched, m, b.scan_sums,
                                                                              g.point_offsets, nullptr, host_total)));

@@ -160,7 +160,8 @@ struct BinningState {         // replaces BinningState (rasterizer_impl.h:57-66)
     uint32_t* tile_keys_tmp;  // [R]
     uint32_t* vals_tmp;       // [R]
     uint32_t* sort_scratch;   // radix-sort tables for the R-sized sort: digit histograms [4][256], tickets, look-back status
-    uint32_t* scan_sums;      // [scan tiles + 8]: look-back words of the tile-count scan, then total (num_rendered), ticket
+    uint32_t* scan_sums;      // [2 * scan tiles + 16]: look-back words of the tile-count scan, total (num_rendered), ticket; from
+                              // [scan tiles + 8] on the plain tile sums of the two-launch scan
     int32_t* tile_diff;       // [(gx + 1) * (gy + 1)] difference array of the tile rectangles (+1 / -1 at the corners); its
                               // 2-D prefix sum is the number of instances per tile (tile table: ranges, digit histograms)
     char* zero_begin;         // [zero_begin, zero_end): what one memset clears before every binning (tickets, status words,
@@ -177,7 +178,7 @@ struct BinningState {         // replaces BinningState (rasterizer_impl.h:57-66)
         b.tile_keys_tmp = carve<uint32_t>(p, Rp);
         b.vals_tmp = carve<uint32_t>(p, Rp);
         b.sort_scratch = carve<uint32_t>(p, sort_scratch_words(R));
-        b.scan_sums = carve<uint32_t>(p, scan_tiles(P) + 8);
+        b.scan_sums = carve<uint32_t>(p, 2 * scan_tiles(P) + 16);   // status words + 8 (total, counter), then the tile sums
         b.tile_diff = carve<int32_t>(p, diff_cells(W, H));
         b.zero_begin = reinterpret_cast<char*>(b.sort_scratch + 4 * GSR_RADIX);
         b.zero_end = reinterpret_cast<char*>(b.tile_diff + diff_cells(W, H));

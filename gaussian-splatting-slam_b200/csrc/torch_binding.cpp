@@ -133,6 +133,7 @@ torch::Tensor sink_or_new(const c10::optional<torch::Tensor>& sink, at::IntArray
 // dL_dscales, dL_drotations, dL_dconic, dL_ddc); entries of inputs that were not supplied -- or that were accumulated
 // into a sink -- are undefined tensors (None in Python). `sinks`: 7 optional tensors in the order (means3D, opacities,
 // colors_precomp, cov3D_precomp, shs, scales, rotations) + dc; when `accumulate` is set every supplied input needs one.
+// `overwrite` (with sinks): the kernel writes the sinks in full instead of adding to them (first view of a batch).
 std::vector<c10::optional<torch::Tensor>> rasterize_gaussians_backward(
     const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii, const torch::Tensor& colors,
     const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations, double scale_modifier,
@@ -140,7 +141,7 @@ std::vector<c10::optional<torch::Tensor>> rasterize_gaussians_backward(
     double tan_fovy, const torch::Tensor& dL_dout_color, const c10::optional<torch::Tensor>& dL_dout_invdepth,
     const torch::Tensor& sh, int64_t degree, const torch::Tensor& campos, const torch::Tensor& geomBuffer, int64_t R,
     const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, bool antialiasing, bool debug, bool want_conic,
-    bool accumulate, const std::vector<c10::optional<torch::Tensor>>& sinks, const torch::Tensor& dc) {
+    bool accumulate, const std::vector<c10::optional<torch::Tensor>>& sinks, const torch::Tensor& dc, bool overwrite) {
     const int64_t P = means3D.size(0), H = dL_dout_color.size(1), W = dL_dout_color.size(2);
     ViewArgs a;
     fill_view(a, background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
@@ -171,7 +172,7 @@ std::vector<c10::optional<torch::Tensor>> rasterize_gaussians_backward(
     if (P != 0) {
         auto wp = [](const torch::Tensor& t) -> float* { return t.defined() && t.numel() ? t.data_ptr<float>() : nullptr; };
         gsr_grads g{wp(dmeans2D), wp(dopacity), wp(dmeans3D), wp(dcolors), wp(dcov), wp(dsh), wp(dscales), wp(drot), wp(dconic),
-                    wp(ddc), accumulate ? 1 : 0, 1};
+                    wp(ddc), (accumulate && !overwrite) ? 1 : 0, 1};   // overwrite: the sinks are written in full
         std::vector<torch::Tensor> keep;
         torch::Tensor dpix = prep(dL_dout_color, "dL_dout_color", keep);
         torch::Tensor dinv = dL_dout_invdepth.has_value() ? prep(*dL_dout_invdepth, "dL_dout_invdepth", keep) : torch::Tensor();

@@ -310,7 +310,9 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
     grad_sinks (superset, multi-view batches): dict of fp32 contiguous CUDA tensors keyed by input name ("means3D",
     "opacities", "shs" | "colors_precomp", "scales" + "rotations" | "cov3D_precomp"), one for EVERY supplied input. The
     gradients of this view are then ADDED into them inside the kernel (gsr_grads.accumulate) and the corresponding
-    returned entries are None; dL_dmeans2D is still returned per view."""
+    returned entries are None; dL_dmeans2D is still returned per view. With the extra entry `"overwrite": True` the sinks
+    are WRITTEN in full instead (zeros for culled Gaussians) -- the first view of a batch then needs no cleared sinks."""
+    overwrite = bool(grad_sinks.get("overwrite", False)) if grad_sinks is not None else False
     ext = torch_ext()
     if ext:
         has_dc = dc is not None and dc.numel() != 0
@@ -322,7 +324,7 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
             bg, means3D, radii, colors, opacity, scales, rotations, float(scale_modifier), cov3D_precomp, viewmatrix,
             projmatrix, float(tan_fovx), float(tan_fovy), dL_dout_color, dL_dout_invdepth, sh, int(degree), campos, geomBuffer,
             int(R), binningBuffer, imageBuffer, bool(antialiasing), bool(debug), bool(want_conic), grad_sinks is not None, sinks,
-            dc if dc is not None else _EMPTY)
+            dc if dc is not None else _EMPTY, overwrite)
         out = tuple(res[:8])
         if want_conic:
             out = out + (res[8],)
@@ -377,7 +379,7 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, opacity, scales, ro
                 _acc_clean[key] = acc
             g = _Grads(_ptr(dL_dmeans2D), _ptr(dL_dopacity), _ptr(dL_dmeans3D), _ptr(dL_dcolors), _ptr(dL_dcov3D),
                        _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drot), _ptr(dL_dconic), _ptr(dL_ddc),
-                       0 if grad_sinks is None else 1, 1)
+                       0 if (grad_sinks is None or overwrite) else 1, 1)
             rc = lib().gsr_backward(C.byref(view), int(R), _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
                                     _ptr(imageBuffer), dpix.data_ptr(), _ptr(dinv), acc.data_ptr(), C.byref(g), stream)
             if rc != 0:

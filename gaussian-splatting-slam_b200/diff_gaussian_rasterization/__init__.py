@@ -146,7 +146,8 @@ class GaussianRasterizer(nn.Module):
         its own [P,1,3] tensor and `shs` = the higher coefficients [P,M-1,3], read in place by the kernels (no
         torch.cat of the features, gaussian_model.py:113-117, and its backward split);
         `grad_sinks` -- a dict of fp32 tensors keyed by input name; the backward then ADDS this view's gradients into
-        them inside the kernel and autograd receives None for those inputs (multi-view batches)."""
+        them inside the kernel and autograd receives None for those inputs (multi-view batches); with the extra entry
+        `"overwrite": True` the sinks are written in full instead (first view of a batch: no cleared sinks needed)."""
         rs = self.raster_settings
         if ((shs is None and dc is None) and colors_precomp is None) or \
                 ((shs is not None or dc is not None) and colors_precomp is not None):

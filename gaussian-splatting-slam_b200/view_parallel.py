@@ -363,6 +363,14 @@ class GradBucket:
     def zero(self):
         self.flat.zero_()
 
+    @property
+    def views_first(self):
+        """grad_sinks for the FIRST view of a step: the backward writes the bucket in full (zeros for culled Gaussians)
+        instead of adding to it, so the step needs no zero() -- 708 MB of stores at 3M Gaussians."""
+        d = dict(self.views)
+        d["overwrite"] = True
+        return d
+
     def nbytes(self) -> int:
         return self.flat.numel() * 4
 

@@ -190,3 +190,54 @@ def test_torch_extension_and_ctypes_bindings_agree():
     _same_state(a, b)
     for k in a["grads"]:
         assert rel_l2(a["grads"][k], b["grads"][k]) <= 1e-5, k
+
+
+@pytest.mark.parametrize("binding", ["torch-extension", "ctypes"])
+def test_grad_sinks_overwrite_on_the_first_view_then_accumulate(binding):
+    """grad_sinks with "overwrite": True writes the sinks in full (zeros for culled Gaussians) whatever they held before;
+    the following views add to them. Two views into NaN-filled sinks == the sum of two plain backward passes."""
+    from diff_gaussian_rasterization import GaussianRasterizer, _C
+    from util import cuda_settings
+    ext = _C.torch_ext()
+    if binding == "torch-extension" and not ext:
+        pytest.skip("_gsr_torch.so not built")
+    sc = _scene(5000, 0.02, 0.25, spread=3.0)                       # wide cloud: a good part is outside the frustum
+    cams = [scenes.look_at_camera(320, 208, math.radians(60), (0.1, -0.2, -3.3)),
+            scenes.look_at_camera(320, 208, math.radians(60), (2.5, 0.3, -2.0))]
+    names = ("means3D", "opacities", "shs", "scales", "rotations")
+    dpix = torch.as_tensor(np.random.default_rng(8).standard_normal((3, 208, 320)).astype(np.float32), device=DEV)
+    try:
+        if binding == "ctypes":
+            _C._ext = False
+        p = {n: getattr(sc, n).to(DEV).requires_grad_(True) for n in names}
+
+        def render(cam, sinks):
+            st = cuda_settings(cam, (0.1, 0.2, 0.3), sc.sh_degree, DEV)
+            color, radii, _ = GaussianRasterizer(st)(means3D=p["means3D"], means2D=torch.zeros_like(p["means3D"]),
+                                                     opacities=p["opacities"], shs=p["shs"], scales=p["scales"],
+                                                     rotations=p["rotations"], grad_sinks=sinks)
+            torch.autograd.backward([color], [dpix])
+            return radii
+        want = {n: torch.zeros_like(p[n]) for n in names}
+        culled_everywhere = torch.ones(p["means3D"].shape[0], dtype=torch.bool, device=DEV)
+        for cam in cams:
+            for t in p.values():
+                t.grad = None
+            radii = render(cam, None)
+            culled_everywhere &= radii == 0
+            for n in names:
+                want[n] += p[n].grad
+        assert int(culled_everywhere.sum()) > 100, "the test needs Gaussians no view sees"
+        sinks = {n: torch.full_like(p[n], float("nan")) for n in names}
+        for t in p.values():
+            t.grad = None
+        render(cams[0], dict(sinks, overwrite=True))
+        render(cams[1], sinks)
+        torch.cuda.synchronize()
+        for n in names:
+            assert p[n].grad is None, "gradients that went into a sink must not reach autograd"
+            assert bool(torch.isfinite(sinks[n]).all()), n
+            assert bool((sinks[n][culled_everywhere] == 0).all()), n
+            assert rel_l2(sinks[n].cpu().numpy(), want[n].cpu().numpy()) <= 1e-5, n
+    finally:
+        _C._ext = ext
