@@ -236,7 +236,9 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
         // A centre that projects near the screen almost always survives the rectangle test below: pull its SH row
         // (192 bytes, two lines) into L2 now, while the covariance is computed. A hint only -- a large splat centred
         // far outside just reads its row from DRAM as before.
-        if (SH16 && fabsf(p_proj.x) < 1.25f && fabsf(p_proj.y) < 1.25f) {
+        // (margin 1.05: at C3 1.441M centres project onto the screen and 1.481M Gaussians are visible; a margin of 1.25
+        // prefetched 1.712M rows -- 44 MB per view for Gaussians that are then culled -- 1.05 prefetches 1.503M)
+        if (SH16 && fabsf(p_proj.x) < 1.05f && fabsf(p_proj.y) < 1.05f) {
             pre_prefetch_l2(a.shs + (size_t)idx * 48);
             pre_prefetch_l2(a.shs + (size_t)idx * 48 + 32);
         }
