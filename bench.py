@@ -810,6 +810,9 @@ def _main(out_fd):
         emit(out_fd, out)
     if ref_world > 1:
         dist.destroy_process_group()
+    if rank == 0 and parity is not None and not parity.get("ok", True):
+        print("bench.py: parity_multi_gpu failed (see the line's parity_multi_gpu field)", file=sys.stderr)
+        return 3                                             # the n-GPU gradients must equal the one-GPU ones
     return 0
 
 

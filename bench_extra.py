@@ -230,27 +230,42 @@ def parity_multi_gpu(arm, args, all_cams, rank, world, dev, rank_dpix):
     if rank == 0:
         exchanged = {k: v.detach().clone() for k, v in arm.bucket.views.items()}
         params = {k: t.detach().clone().requires_grad_(True) for k, t in arm.params.items()}
-        solo = GradBucket(params, exchange="nccl")                  # plain device memory, no collective in the constructor
         m2 = torch.zeros_like(params["means3D"], requires_grad=True)
         n_views = len(all_cams)
-        for r in range(world):                                      # rank by rank: one dL/dpixel image resident at a time
-            dpix = rank_dpix(args, r).to(dev)
-            for i in shard_views(n_views, r, world):
-                cam = all_cams[i]
-                st = arm._settings(cam, cam.viewmatrix.to(dev), cam.projmatrix.to(dev), cam.campos.to(dev))
-                color, _radii, _ = arm.Rasterizer(st)(means3D=params["means3D"], means2D=m2, opacities=params["opacities"],
-                                                      shs=params["shs"], scales=params["scales"], rotations=params["rotations"],
-                                                      grad_sinks=solo.views)
-                torch.autograd.backward([color], [dpix])
-        torch.cuda.synchronize()
-        rel = {}
-        for k, v in solo.views.items():
-            d = (exchanged[k].double() - v.double()).norm()
-            rel[k] = float(d / v.double().norm().clamp_min(1e-30))
+
+        def solo_pass():
+            solo = GradBucket(params, exchange="nccl")              # plain device memory, no collective in the constructor
+            for r in range(world):                                  # rank by rank: one dL/dpixel image resident at a time
+                dpix = rank_dpix(args, r).to(dev)
+                for i in shard_views(n_views, r, world):
+                    cam = all_cams[i]
+                    st = arm._settings(cam, cam.viewmatrix.to(dev), cam.projmatrix.to(dev), cam.campos.to(dev))
+                    color, _radii, _ = arm.Rasterizer(st)(means3D=params["means3D"], means2D=m2, opacities=params["opacities"],
+                                                          shs=params["shs"], scales=params["scales"], rotations=params["rotations"],
+                                                          grad_sinks=solo.views)
+                    torch.autograd.backward([color], [dpix])
+            torch.cuda.synchronize()
+            return solo
+
+        def rel_of(a, b):
+            return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+        solo = solo_pass()
+        rel = {k: rel_of(exchanged[k], v) for k, v in solo.views.items()}
+        # The noise floor of the comparison itself: the SAME one-GPU pass a second time. The blend accumulates with float
+        # atomics, so two passes over identical views differ by the order of additions; on tensors whose per-view terms
+        # cancel (rotations, scales) that alone reaches 1e-5 .. 1e-4 of the sum's norm. The n-GPU result passes when it is
+        # within the bar, or -- where the one-GPU pass cannot reproduce ITSELF to the bar -- within 3x that floor.
+        again = solo_pass()
+        floor = {k: rel_of(again.views[k], v) for k, v in solo.views.items()}
+        ok = all(rel[k] <= max(1e-4, 3.0 * floor[k]) for k in rel)
         res.update({"rel_l2_per_tensor": {k: float(f"{x:.3e}") for k, x in rel.items()}, "max": float(f"{max(rel.values()):.3e}"),
-                    "views_checked": n_views, "bar": 1e-4,
+                    "one_gpu_repeat_rel_l2_per_tensor": {k: float(f"{x:.3e}") for k, x in floor.items()},
+                    "views_checked": n_views, "bar": 1e-4, "ok": bool(ok and identical),
                     "how": "rank 0 renders all views of the step alone (in-kernel accumulation, same kernels) and compares "
-                           "with the bucket the exchange left on it; checksums of the raw bucket words compared over all ranks"})
+                           "with the bucket the exchange left on it; the same one-GPU pass repeated gives the float-atomic "
+                           "noise floor of the comparison (pass: <= bar, or <= 3x that floor); checksums of the raw bucket "
+                           "words compared over all ranks"})
+        del again
         del solo, params, exchanged
         torch.cuda.empty_cache()
     dist.barrier()
