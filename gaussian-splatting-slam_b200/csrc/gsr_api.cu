@@ -693,6 +693,29 @@ int gsr_debug_set_exact_cull(int on) { return set_exact_cull(on); }
 int gsr_debug_set_blend_variant(int v) { return set_blend_variant(v); }
 int gsr_debug_set_comm_variant(int v) { return set_comm_variant(v); }
 
+// Test hook: the library's own stable radix sort of (key, value) pairs on key bits [0, total_bits), as the depth sort
+// (drop != 0: keys 0xFFFFFFFF are dropped, *n_valid_out = pairs kept), the Morton sort of distCUDA2 and the instance sort
+// use it. Sorted pairs end up in (keys, vals). scratch: gsr_debug_sort_scratch_bytes(n) bytes.
+size_t gsr_debug_sort_scratch_bytes(int n) { return sizeof(uint32_t) * sort_scratch_words((size_t)(n > 0 ? n : 1)); }
+int gsr_debug_sort_pairs(uint32_t* keys, uint32_t* vals, uint32_t* keys_tmp, uint32_t* vals_tmp, int n, int total_bits, int drop,
+                         uint32_t* scratch, uint32_t* n_valid_out, void* stream) {
+    if (n < 0 || total_bits < 0 || total_bits > 32 || (n > 0 && (!keys || !vals || !keys_tmp || !vals_tmp || !scratch)))
+        return GSR_E_BADARG;
+    if (drop && !n_valid_out) return GSR_E_BADARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    bool in_a = true;
+    uint32_t* n_dev = nullptr;
+    const int e = radix_sort_u32(keys, vals, keys_tmp, vals_tmp, n, total_bits, scratch, &in_a, false, s, drop ? &n_dev : nullptr);
+    if (e) return e;
+    cudaError_t ce = cudaSuccess;
+    if (!in_a && n > 0) {
+        ce = cudaMemcpyAsync(keys, keys_tmp, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToDevice, s);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(vals, vals_tmp, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToDevice, s);
+    }
+    if (ce == cudaSuccess && drop && n > 0) ce = cudaMemcpyAsync(n_valid_out, n_dev, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s);
+    return (int)ce;
+}
+
 int gsr_debug_fp32_peak(int iters, float* out, int* sms_out, void* stream) {
     if (iters <= 0 || !out) return GSR_E_BADARG;
     return launch_fp32_peak(iters, out, sms_out, (cudaStream_t)stream);

@@ -317,6 +317,106 @@ __global__ void __launch_bounds__(kSortThreads, kSortCtasPerSm) onesweep_kernel(
     }
 }
 
+// ------------------------------------------------------------------ small sorts: every pass in ONE CTA
+// Up to kSmallMax pairs (config 1's 10k Gaussians, a SLAM keyframe's new points): the multi-launch sort costs a histogram
+// kernel plus one latency-bound launch per pass (4 x 11 us + 14 us at 10k keys, a quarter of config 1's view). Here one
+// CTA of 1024 threads holds all pairs in registers (12 per thread, warp-striped order) and runs every pass through shared
+// memory: per-warp digit counters by the same ballot ranking as the tiles above, digit-major / warp-minor prefix, scatter,
+// read back. Slots beyond n carry the key 0xFFFFFFFF, which sorts behind everything in every pass (ties keep input order:
+// real keys first), so there is no validity mask anywhere; drop mode only counts the keys that are not 0xFFFFFFFF.
+constexpr int kSmallThreads = 1024, kSmallItems = 12, kSmallMax = kSmallThreads * kSmallItems;   // 12288
+constexpr int kSmallWarps = kSmallThreads / 32;
+struct SmallSortSmem {
+    uint32_t keys[kSmallMax];
+    uint32_t vals[kSmallMax];
+    uint32_t whist[kSmallWarps][GSR_RADIX];
+    uint32_t dsum[GSR_RADIX];
+    uint32_t warp_sums[8];
+    uint32_t kept[kSmallWarps];
+};
+__global__ void __launch_bounds__(kSmallThreads, 1) small_sort_kernel(uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, int n,
+                                                                      int total_bits, uint32_t* __restrict__ n_valid_out) {
+    extern __shared__ __align__(16) unsigned char small_smem_raw[];
+    SmallSortSmem& sm = *reinterpret_cast<SmallSortSmem*>(small_smem_raw);
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const int wofs = w * (32 * kSmallItems) + lane;            // order index of item i: wofs + 32 * i
+    uint32_t key[kSmallItems], val[kSmallItems];
+    uint32_t kept = 0;
+#pragma unroll
+    for (int i = 0; i < kSmallItems; i++) {
+        const int idx = wofs + 32 * i;
+        key[i] = idx < n ? keys[idx] : 0xFFFFFFFFu;
+        val[i] = idx < n ? vals[idx] : 0u;
+        kept += key[i] != 0xFFFFFFFFu;
+    }
+    if (n_valid_out != nullptr) {                               // drop mode: how many pairs are part of the result
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) kept += __shfl_xor_sync(kAll, kept, o);
+        if (lane == 0) sm.kept[w] = kept;
+    }
+    const int passes = (total_bits + 7) / 8;
+    for (int p = 0; p < passes; p++) {
+        const int shift = 8 * p;
+        const uint32_t mask = (total_bits - shift) >= 8 ? 255u : ((1u << (total_bits - shift)) - 1u);
+        for (int i = t; i < kSmallWarps * GSR_RADIX; i += kSmallThreads) (&sm.whist[0][0])[i] = 0u;
+        __syncthreads();
+        uint32_t rank[kSmallItems];
+#pragma unroll
+        for (int i = 0; i < kSmallItems; i++) {
+            const uint32_t d = (key[i] >> shift) & mask;
+            const uint32_t peers = same_digit_lanes<8>(d, kAll);
+            const int leader = __ffs(peers) - 1;
+            uint32_t prev = 0;
+            if (lane == leader) prev = atomicAdd(&sm.whist[w][d], (uint32_t)__popc(peers));   // one warp: program order
+            prev = __shfl_sync(kAll, prev, leader);
+            rank[i] = prev + __popc(peers & lt_mask);
+        }
+        __syncthreads();
+        // digit t (threads 0..255): total over the warps, exclusive scan over the digits, start of every (warp, digit) run
+        uint32_t run = 0;
+        if (t < GSR_RADIX) {
+#pragma unroll 8
+            for (int k = 0; k < kSmallWarps; k++) run += sm.whist[k][t];
+        }
+        if (t < GSR_RADIX) {                                    // warps 0..7 are whole: shuffles are safe
+            uint32_t incl = run;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(kAll, incl, o);
+                if (lane >= o) incl += y;
+            }
+            if (lane == 31) sm.warp_sums[w] = incl;
+            sm.dsum[t] = incl - run;                            // exclusive inside the warp of digits
+        }
+        __syncthreads();
+        if (t < GSR_RADIX) {
+            uint32_t acc = sm.dsum[t];
+            for (int k = 0; k < w; k++) acc += sm.warp_sums[k];
+#pragma unroll 8
+            for (int k = 0; k < kSmallWarps; k++) { const uint32_t c = sm.whist[k][t]; sm.whist[k][t] = acc; acc += c; }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < kSmallItems; i++) {
+            const uint32_t pos = sm.whist[w][(key[i] >> shift) & mask] + rank[i];
+            sm.keys[pos] = key[i];
+            sm.vals[pos] = val[i];
+        }
+        __syncthreads();
+        if (p + 1 < passes) {
+#pragma unroll
+            for (int i = 0; i < kSmallItems; i++) { key[i] = sm.keys[wofs + 32 * i]; val[i] = sm.vals[wofs + 32 * i]; }
+        }
+    }
+    for (int idx = t; idx < n; idx += kSmallThreads) { keys[idx] = sm.keys[idx]; vals[idx] = sm.vals[idx]; }
+    if (n_valid_out != nullptr && t == 0) {
+        uint32_t tot = 0;
+        for (int k = 0; k < kSmallWarps; k++) tot += sm.kept[k];
+        *n_valid_out = tot;
+    }
+}
+
 template <int BITS, int MODE = 0, bool WRITE_KEYS = true>
 static int launch_pass(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, int n, int shift,
                        const uint32_t* ghist, uint32_t* ticket, uint32_t* status, int tiles, cudaStream_t s,
@@ -347,6 +447,8 @@ static int launch_pass_bits(int bits, const uint32_t* kin, const uint32_t* vin, 
     }
 }
 
+static int g_small_sort = [] { const char* e = getenv("GSR_SMALL_SORT"); return e ? atoi(e) : 1; }();    // A/B switch
+
 int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n, int total_bits, uint32_t* scratch,
                    bool* result_in_a, bool debug, cudaStream_t s, uint32_t** n_valid_dev, bool scratch_zeroed,
                    const SortOptions* opt) {
@@ -361,6 +463,13 @@ int radix_sort_u32(uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int n
     *result_in_a = true;
     if (drop) *n_valid_dev = scratch + 4 * GSR_RADIX + 8;          // a spare word of the ticket block (zeroed below)
     if (n <= 0 || total_bits <= 0) return 0;
+    if (n <= kSmallMax && opt == nullptr && g_small_sort) {        // every pass in one CTA, in place in (ka, va)
+        static DeviceOnce once_small;
+        { const int e = ensure_dynamic_smem(small_sort_kernel, (int)sizeof(SmallSortSmem), once_small); if (e) return e; }
+        GSR_LAUNCH("small_sort", debug, s,
+                   (small_sort_kernel<<<1, kSmallThreads, sizeof(SmallSortSmem), s>>>(ka, va, n, total_bits, drop ? *n_valid_dev : nullptr)));
+        return 0;
+    }
     const int passes = radix_passes(total_bits);
     const int tiles = (int)sort_tiles((size_t)n);
     uint32_t* ghist = scratch;                                  // [4][256]
