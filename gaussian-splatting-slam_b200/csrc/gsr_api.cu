@@ -213,6 +213,7 @@ std::mutex g_hint_mu;
 std::vector<CapHint> g_hints;
 int g_speculate = -1;                        // -1: read GSR_SPECULATE on first use
 int g_overlap = 1;                           // tile table on a side stream under the depth sort (gsr_set_speculation(2) = off)
+int g_split = -1;                            // colour half of the preprocess off the critical path: OFF unless GSR_SPLIT_PRE=1
 unsigned long long g_spec_hits = 0, g_spec_retries = 0, g_spec_cold = 0;
 
 bool speculation_on() {
@@ -221,6 +222,13 @@ bool speculation_on() {
         g_speculate = (e && e[0] == '0') ? 0 : 1;
     }
     return g_speculate != 0;
+}
+bool split_on() {
+    if (g_split < 0) {
+        const char* e = getenv("GSR_SPLIT_PRE");
+        g_split = (e && e[0] == '1') ? 1 : 0;
+    }
+    return g_split != 0;
 }
 uint32_t hint_capacity(int dev, int W, int H, int P) {
     std::lock_guard<std::mutex> lk(g_hint_mu);
@@ -256,19 +264,27 @@ struct CountSlot {
     cudaEvent_t ev[kMaxDevices] = {};
     bool have[kMaxDevices] = {};
     cudaStream_t side_stream[kMaxDevices] = {};
-    cudaEvent_t fork_ev[kMaxDevices] = {}, join_ev[kMaxDevices] = {};
+    cudaStream_t chain_stream[kMaxDevices] = {};   // highest priority: the latency-bound binning chain of the split forward
+    cudaEvent_t fork_ev[kMaxDevices] = {}, join_ev[kMaxDevices] = {}, chain_ev[kMaxDevices] = {};
     int side_state[kMaxDevices] = {};      // 0 = not created, 1 = ready, -1 = creation failed (stay in-stream)
-    int side(int dev, cudaStream_t* st, cudaEvent_t* fork, cudaEvent_t* join) {
+    int side(int dev, cudaStream_t* st, cudaEvent_t* fork, cudaEvent_t* join, cudaStream_t* chain = nullptr,
+             cudaEvent_t* chain_done = nullptr) {
         if (dev < 0 || dev >= kMaxDevices) return GSR_E_BADARG;
         if (side_state[dev] == 0) {
-            cudaError_t ce = cudaStreamCreateWithFlags(&side_stream[dev], cudaStreamNonBlocking);
+            int least = 0, greatest = 0;
+            cudaError_t ce = cudaDeviceGetStreamPriorityRange(&least, &greatest);
+            if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&side_stream[dev], cudaStreamNonBlocking);
+            if (ce == cudaSuccess) ce = cudaStreamCreateWithPriority(&chain_stream[dev], cudaStreamNonBlocking, greatest);
             if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&fork_ev[dev], cudaEventDisableTiming);
             if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&join_ev[dev], cudaEventDisableTiming);
+            if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&chain_ev[dev], cudaEventDisableTiming);
             side_state[dev] = ce == cudaSuccess ? 1 : -1;
             if (ce != cudaSuccess) (void)cudaGetLastError();
         }
         if (side_state[dev] != 1) return GSR_E_BADARG;
         *st = side_stream[dev]; *fork = fork_ev[dev]; *join = join_ev[dev];
+        if (chain) *chain = chain_stream[dev];
+        if (chain_done) *chain_done = chain_ev[dev];
         return 0;
     }
     int get(int dev, cudaEvent_t* e) {
@@ -356,6 +372,18 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
     char* bp = nullptr;
     bool table_done = false, binning_zeroed = false;
     cudaEvent_t ev_join = nullptr;
+    // Split forward -- MEASURED AND NOT ADOPTED (GSR_SPLIT_PRE=1 enables it; C3: 1.878 against 1.863 ms/view, SLAM loop 0.771
+    // against 0.741 ms/keyframe): the colour kernel saturates HBM while it runs, the latency-bound chain kernels beside it
+    // slow down by what the overlap was meant to save (histogram 21 -> 59 us, depth passes 95 -> 128 us, tile table 41 ->
+    // 178 us) and the colour pass itself takes 135 us without the L2 prefetch distance the one-kernel preprocess gives it.
+    // The design: (estimate known, side streams available) the geometry half of the preprocess runs on the caller's
+    // stream; the binning chain (histogram, depth passes, scan, emission, instance sort -- latency- and issue-bound, little
+    // HBM traffic) moves to a library-owned stream of the HIGHEST priority, the tile table to the side stream, and the
+    // colour half of the preprocess (60 % of its bytes) stays on the caller's stream, where it runs UNDER the chain: the
+    // chain's CTAs take SM slots first whenever some free up. The caller's stream joins the chain before the blend.
+    cudaStream_t cs = s;                                              // stream of the binning chain
+    cudaEvent_t ev_chain = nullptr;
+    bool chain_forked = false;
     void* za = nullptr; size_t zan = 0;
     depth_sort_zero_region(g, &za, &zan);
     if (!cold) {
@@ -363,29 +391,41 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
         if (!bp) return GSR_E_ALLOC;
         char* bq = bp;                                                // from() advances the pointer it is given
         BinningState b0 = BinningState::from(bq, (size_t)cap, (size_t)v.P, v.W, v.H);
-        e = launch_preprocess(v, g, radii, s, za, zan, b0.zero_begin, (size_t)(b0.zero_end - b0.zero_begin));
+        cudaStream_t side = nullptr, chain = nullptr;
+        cudaEvent_t ev_fork = nullptr;
+        const bool have_side = g_overlap && !v.debug && t_slot.side(dev, &side, &ev_fork, &ev_join, &chain, &ev_chain) == 0;
+        const bool split = have_side && split_on();
+        e = launch_preprocess(v, g, radii, s, za, zan, b0.zero_begin, (size_t)(b0.zero_end - b0.zero_begin), split);
         if (e) return e;
         binning_zeroed = true;
-        cudaStream_t side = nullptr;
-        cudaEvent_t ev_fork = nullptr;
-        if (g_overlap && !v.debug && t_slot.side(dev, &side, &ev_fork, &ev_join) == 0) {
+        if (have_side) {
             cudaError_t ce = cudaEventRecord(ev_fork, s);
             if (ce == cudaSuccess) ce = cudaStreamWaitEvent(side, ev_fork, 0);
+            if (ce == cudaSuccess && split) ce = cudaStreamWaitEvent(chain, ev_fork, 0);
             if (ce != cudaSuccess) return (int)ce;
+            if (split) { cs = chain; chain_forked = true; }
             e = launch_tile_table(v, g, radii, b0, img, side, /*scratch_zeroed=*/true);
             if (e) return e;
             ce = cudaEventRecord(ev_join, side);
             if (ce != cudaSuccess) return (int)ce;
             table_done = true;
         }
+        if (split) {
+            e = launch_depth_order(v, g, cs, /*scratch_zeroed=*/true);     // chain stream first: its kernels are queued ahead
+            if (e) return e;
+            e = launch_preprocess_color(v, g, radii, s);
+            if (e) return e;
+        }
     } else {
         e = launch_preprocess(v, g, radii, s, za, zan);
         if (e) return e;
     }
-    e = launch_depth_order(v, g, s, /*scratch_zeroed=*/true);
-    if (e) return e;
+    if (!chain_forked) {
+        e = launch_depth_order(v, g, s, /*scratch_zeroed=*/true);
+        if (e) return e;
+    }
     if (table_done) {
-        cudaError_t ce = cudaStreamWaitEvent(s, ev_join, 0);
+        cudaError_t ce = cudaStreamWaitEvent(cs, ev_join, 0);
         if (ce != cudaSuccess) return (int)ce;
     }
     if (cold) {
@@ -409,8 +449,9 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
         BinningState b = BinningState::from(bq, (size_t)cap, (size_t)v.P, v.W, v.H);
         bp = nullptr;                                                 // a repeat allocates a new blob
         uint32_t* total_dev = nullptr;
+        const cudaStream_t bs = attempt == 0 ? cs : s;                // a repeat runs on the caller's stream (already joined)
         if (!table_done) {
-            e = launch_tile_table(v, g, radii, b, img, s, binning_zeroed);
+            e = launch_tile_table(v, g, radii, b, img, bs, binning_zeroed);
             if (e) return e;
         }
         table_done = false;
@@ -418,8 +459,13 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
         const bool check_count = !cold || attempt > 0 || v.debug;
         constexpr uint32_t kPending = 0xFFFFFFFFu;
         if (check_count) *(volatile uint32_t*)t_slot.host = kPending;
-        e = launch_binning(v, g, radii, b, img, cap, &total_dev, check_count && cap > 0 ? t_slot.host_dev : nullptr, s);
+        e = launch_binning(v, g, radii, b, img, cap, &total_dev, check_count && cap > 0 ? t_slot.host_dev : nullptr, bs);
         if (e) return e;
+        if (attempt == 0 && chain_forked) {                           // the caller's stream (colours) meets the chain (lists)
+            cudaError_t ce = cudaEventRecord(ev_chain, cs);
+            if (ce == cudaSuccess) ce = cudaStreamWaitEvent(s, ev_chain, 0);
+            if (ce != cudaSuccess) return (int)ce;
+        }
         e = launch_blend_forward(v, g, b.point_list, img, out_color, out_invdepth, cold && attempt == 0 ? nullptr : total_dev, cap, s);
         if (e) return e;
         if (!check_count) break;                                      // exact capacity: nothing to check
@@ -428,7 +474,7 @@ int gsr_forward(const gsr_view* view, gsr_alloc_fn geom_alloc, void* geom_ctx, g
         uint32_t got = cap > 0 ? *(volatile uint32_t*)t_slot.host : 0u;
         for (unsigned spins = 0; got == kPending; spins++) {
             if ((spins & 1023u) == 1023u) {
-                const cudaError_t q = cudaStreamQuery(s);
+                const cudaError_t q = cudaStreamQuery(bs);
                 if (q != cudaErrorNotReady) {                         // the stream has drained (or failed): one last look
                     got = *(volatile uint32_t*)t_slot.host;
                     if (got == kPending) return q != cudaSuccess ? (int)q : GSR_E_BADARG;

@@ -208,8 +208,10 @@ static inline uint32_t higher_msb(uint32_t n) {   // rasterizer_impl.cu:35-50
 
 // ---------------------------------------------------------------- stage entry points (host)
 // zero_a / zero_b: optional scratch regions (multiples of 4 bytes) the kernel zero-fills on the side
+// geometry_only: colours / inverse depths / clamp bits are left to launch_preprocess_color (any stream, after this one)
 int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s, void* zero_a = nullptr,
-                      size_t zero_a_bytes = 0, void* zero_b = nullptr, size_t zero_b_bytes = 0);
+                      size_t zero_a_bytes = 0, void* zero_b = nullptr, size_t zero_b_bytes = 0, bool geometry_only = false);
+int launch_preprocess_color(const gsr_view& v, GeomState& g, const int* radii, cudaStream_t s);
 int launch_mark_visible(int P, const float* means, const float* view, uint8_t* present, cudaStream_t s);
 // depth-order the visible Gaussians (drop-mode radix sort; the visible count stays on the device)
 int launch_depth_order(const gsr_view& v, GeomState& g, cudaStream_t s, bool scratch_zeroed = false);

@@ -188,7 +188,10 @@ struct PreArgs {
     uint32_t* zero_b; long long zero_b_words;
 };
 
-template <bool SH16>
+// GEOM_ONLY: the colour (SH evaluation, the 192-byte row per visible Gaussian) and the clamp bits are left to
+// preprocess_color_kernel, which gsr_forward runs on a side stream UNDER the latency-bound depth sort / scan / instance
+// sort: nothing before the blend needs the colours, and they are 60 % of this kernel's bytes.
+template <bool SH16, bool GEOM_ONLY>
 __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a, int* __restrict__ radii,
                                                               float* __restrict__ depths, float4* __restrict__ rec,
                                                               float4* __restrict__ colr,
@@ -238,7 +241,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
         // far outside just reads its row from DRAM as before.
         // (margin 1.05: at C3 1.441M centres project onto the screen and 1.481M Gaussians are visible; a margin of 1.25
         // prefetched 1.712M rows -- 44 MB per view for Gaussians that are then culled -- 1.05 prefetches 1.503M)
-        if (SH16 && fabsf(p_proj.x) < 1.05f && fabsf(p_proj.y) < 1.05f) {
+        if (!GEOM_ONLY && SH16 && fabsf(p_proj.x) < 1.05f && fabsf(p_proj.y) < 1.05f) {
             pre_prefetch_l2(a.shs + (size_t)idx * 48);
             pre_prefetch_l2(a.shs + (size_t)idx * 48 + 32);
         }
@@ -266,14 +269,16 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
         tile_rect(point_image, my_radius, rect_min, rect_max, grid);
         if ((rect_max.x - rect_min.x) * (rect_max.y - rect_min.y) == 0) break;
 
-        V3 color;
+        V3 color = {0.f, 0.f, 0.f};
         uint8_t cb = 0;
-        if (a.colors_precomp == nullptr) {      // SH input (fused, or dc + rest)
-            color = sh_color<SH16>(idx, a.D, a.M, V3{p_orig.x, p_orig.y, p_orig.z},
-                                   V3{__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2)}, a.shs, a.sh_dc, cb);
-        } else {
-            color = {__ldg(a.colors_precomp + 3 * idx), __ldg(a.colors_precomp + 3 * idx + 1),
-                     __ldg(a.colors_precomp + 3 * idx + 2)};
+        if (!GEOM_ONLY) {
+            if (a.colors_precomp == nullptr) {      // SH input (fused, or dc + rest)
+                color = sh_color<SH16>(idx, a.D, a.M, V3{p_orig.x, p_orig.y, p_orig.z},
+                                       V3{__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2)}, a.shs, a.sh_dc, cb);
+            } else {
+                color = {__ldg(a.colors_precomp + 3 * idx), __ldg(a.colors_precomp + 3 * idx + 1),
+                         __ldg(a.colors_precomp + 3 * idx + 2)};
+            }
         }
         float opacity = opacity_in;
         if (a.antialiasing) opacity = opacity * sqrtf(fmaxf(0.000025f, det_cov / det));   // dr_aa (F1)
@@ -294,7 +299,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
         my_radii = my_radius;
         rec[2 * (size_t)idx + 0] = make_float4(point_image.x, point_image.y, ex, ey);
         rec[2 * (size_t)idx + 1] = make_float4(conic.x, conic.y, conic.z, opacity);
-        colr[idx] = make_float4(color.x, color.y, color.z, 1.0f / p_view.z);
+        if (!GEOM_ONLY) colr[idx] = make_float4(color.x, color.y, color.z, 1.0f / p_view.z);
         my_clamp = cb;
         my_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
         // the rectangle itself, for the scan and the instance emission (binning): they then need neither the record nor
@@ -309,8 +314,34 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a,
     dkey[idx] = my_key;
     order[idx] = (uint32_t)idx;
     depths[idx] = my_depth;
-    clamped[idx] = my_clamp;
+    if (!GEOM_ONLY) clamped[idx] = my_clamp;
     rect_packed[idx] = my_rect;
+}
+
+// The colour half of the forward preprocess (see GEOM_ONLY above): colour from SH (or the precomputed one) + inverse depth
+// for every visible Gaussian, clamp bits for all. Visibility and depth come from the geometry pass (radii, depths), so the
+// inverse depth has the same bits as in the one-kernel path.
+template <bool SH16>
+__global__ void __launch_bounds__(256, 4) preprocess_color_kernel(const PreArgs a, const int* __restrict__ radii,
+                                                                  const float* __restrict__ depths, float4* __restrict__ colr,
+                                                                  uint8_t* __restrict__ clamped) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= a.P) return;
+    uint8_t cb = 0;
+    if (__ldg(radii + idx) > 0) {
+        const float depth = __ldg(depths + idx);
+        V3 color;
+        if (a.colors_precomp == nullptr) {
+            const V3 p_orig = {__ldg(a.means3D + 3 * idx), __ldg(a.means3D + 3 * idx + 1), __ldg(a.means3D + 3 * idx + 2)};
+            color = sh_color<SH16>(idx, a.D, a.M, p_orig, V3{__ldg(a.campos), __ldg(a.campos + 1), __ldg(a.campos + 2)}, a.shs,
+                                   a.sh_dc, cb);
+        } else {
+            color = {__ldg(a.colors_precomp + 3 * idx), __ldg(a.colors_precomp + 3 * idx + 1),
+                     __ldg(a.colors_precomp + 3 * idx + 2)};
+        }
+        colr[idx] = make_float4(color.x, color.y, color.z, 1.0f / depth);
+    }
+    clamped[idx] = cb;
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means, const float* __restrict__ view,
@@ -769,7 +800,7 @@ static bool sh16_fast(const gsr_view& v) {
 }
 
 int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t s, void* zero_a, size_t zero_a_bytes,
-                      void* zero_b, size_t zero_b_bytes) {
+                      void* zero_b, size_t zero_b_bytes, bool geometry_only) {
     PreArgs a;
     fill_pre_args(v, a);
     a.zero_a = reinterpret_cast<uint32_t*>(zero_a); a.zero_a_words = (long long)(zero_a_bytes / 4);
@@ -777,12 +808,31 @@ int launch_preprocess(const gsr_view& v, GeomState& g, int* radii, cudaStream_t 
     constexpr int kThreads = 128;
     const int blocks = (v.P + kThreads - 1) / kThreads;
     uint32_t* tiles_touched = rect_packing_ok(v.W, v.H) ? nullptr : g.tiles_touched;
-    if (sh16_fast(v))
+    if (geometry_only)
+        GSR_LAUNCH("preprocess_geom", v.debug, s,
+                   (preprocess_fwd_kernel<false, true><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.colr, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
+    else if (sh16_fast(v))
         GSR_LAUNCH("preprocess_fwd", v.debug, s,
-                   (preprocess_fwd_kernel<true><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.colr, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
+                   (preprocess_fwd_kernel<true, false><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.colr, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
     else
         GSR_LAUNCH("preprocess_fwd", v.debug, s,
-                   (preprocess_fwd_kernel<false><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.colr, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
+                   (preprocess_fwd_kernel<false, false><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.rec, g.colr, g.clamped, tiles_touched, g.dkey, g.order, g.rect_packed)));
+    return 0;
+}
+
+// after launch_preprocess(..., geometry_only = true) on the same data: colours, inverse depths, clamp bits
+int launch_preprocess_color(const gsr_view& v, GeomState& g, const int* radii, cudaStream_t s) {
+    PreArgs a;
+    fill_pre_args(v, a);
+    a.zero_a = nullptr; a.zero_a_words = 0; a.zero_b = nullptr; a.zero_b_words = 0;
+    constexpr int kThreads = 128;
+    const int blocks = (v.P + kThreads - 1) / kThreads;
+    if (sh16_fast(v))
+        GSR_LAUNCH("preprocess_color", v.debug, s,
+                   (preprocess_color_kernel<true><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.colr, g.clamped)));
+    else
+        GSR_LAUNCH("preprocess_color", v.debug, s,
+                   (preprocess_color_kernel<false><<<blocks, kThreads, 0, s>>>(a, radii, g.depths, g.colr, g.clamped)));
     return 0;
 }
 
