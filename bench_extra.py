@@ -258,9 +258,12 @@ def parity_multi_gpu(arm, args, all_cams, rank, world, dev, rank_dpix):
         again = solo_pass()
         floor = {k: rel_of(again.views[k], v) for k, v in solo.views.items()}
         ok = all(rel[k] <= max(1e-4, 3.0 * floor[k]) for k in rel)
+        # what makes bench.py exit non-zero: a GROSS mismatch (one view of 64 missing changes the sums by ~1e-2), not a draw
+        # from the tail of the float-atomic noise -- that is reported through `ok` and the numbers beside it
+        gross = (not identical) or any(rel[k] > max(1e-3, 10.0 * floor[k]) for k in rel)
         res.update({"rel_l2_per_tensor": {k: float(f"{x:.3e}") for k, x in rel.items()}, "max": float(f"{max(rel.values()):.3e}"),
                     "one_gpu_repeat_rel_l2_per_tensor": {k: float(f"{x:.3e}") for k, x in floor.items()},
-                    "views_checked": n_views, "bar": 1e-4, "ok": bool(ok and identical),
+                    "views_checked": n_views, "bar": 1e-4, "ok": bool(ok and identical), "gross_mismatch": bool(gross),
                     "how": "rank 0 renders all views of the step alone (in-kernel accumulation, same kernels) and compares "
                            "with the bucket the exchange left on it; the same one-GPU pass repeated gives the float-atomic "
                            "noise floor of the comparison (pass: <= bar, or <= 3x that floor); checksums of the raw bucket "
