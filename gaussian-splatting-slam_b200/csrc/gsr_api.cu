@@ -312,6 +312,7 @@ struct CountSlot {
 thread_local CountSlot t_slot;
 }  // namespace
 
+int gsr_debug_set_split_forward(int on) { g_split = on ? 1 : 0; return 0; }
 int gsr_set_speculation(int on) { g_speculate = on ? 1 : 0; g_overlap = on == 2 ? 0 : 1; return 0; }
 int gsr_reset_capacity_hints(void) {
     std::lock_guard<std::mutex> lk(g_hint_mu);

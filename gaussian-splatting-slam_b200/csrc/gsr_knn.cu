@@ -190,22 +190,26 @@ __device__ __forceinline__ float box_gap2(const float* r, const float4& bmin, co
     return gx * gx + gy * gy + gz * gz;
 }
 
-constexpr int kStage = 4;      // sub-boxes staged per round (kStage * kSub = one point per thread)
-__global__ void __launch_bounds__(256) knn_kernel(int P, const float4* __restrict__ sorted, const float4* __restrict__ boxes,
+// B = threads (= consecutive Morton-ordered points) per CTA: 256 for large clouds, 64 for small ones (a SLAM keyframe's
+// 25k new points make 98 CTAs of 256 -- fewer than SMs, each a long serial chain of staging rounds -- but 391 CTAs of 64
+// with tighter bounding boxes). kStage = B / kSub sub-boxes are staged per round (one point per thread).
+template <int B>
+__global__ void __launch_bounds__(B) knn_kernel(int P, const float4* __restrict__ sorted, const float4* __restrict__ boxes,
                                                    int nb, const float4* __restrict__ sub, int nsub, float* __restrict__ out) {
-    __shared__ float4 s_pts[256];
+    constexpr int kStage = B / kSub;
+    __shared__ float4 s_pts[B];
     __shared__ float4 s_sb[kStage][2];
-    __shared__ int s_c1[256], s_c0[256];
+    __shared__ int s_c1[B], s_c0[B];
     __shared__ int s_n1, s_n0;
-    __shared__ float s_red[7][8];
+    __shared__ float s_red[7][B / 32];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const int cbase = blockIdx.x * 256;
+    const int cbase = blockIdx.x * B;
     const int pos = cbase + tid;
     const bool valid = pos < P;
     const float4 me = valid ? __ldg(sorted + pos) : make_float4(0.f, 0.f, 0.f, 0.f);
     float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
-    // ---- phase 1: the CTA's own 256 points (4 sub-boxes), brute force. These are real candidates.
-    const int own = min(256, P - cbase);
+    // ---- phase 1: the CTA's own B points (B / 64 sub-boxes), brute force. These are real candidates.
+    const int own = min(B, P - cbase);
     s_pts[tid] = me;
     __syncthreads();
     if (valid) {
@@ -227,17 +231,17 @@ __global__ void __launch_bounds__(256) knn_kernel(int P, const float4* __restric
     if (lane == 0)
         for (int a = 0; a < 7; a++) s_red[a][w] = r[a];
     __syncthreads();
-    for (int k = 0; k < 8; k++) {
+    for (int k = 0; k < B / 32; k++) {
 #pragma unroll
         for (int a = 0; a < 3; a++) r[a] = fminf(r[a], s_red[a][k]);
 #pragma unroll
         for (int a = 3; a < 7; a++) r[a] = fmaxf(r[a], s_red[a][k]);
     }
     const float rmax = r[6];
-    const int own_sb0 = cbase / kSub, own_sb1 = own_sb0 + 256 / kSub;      // sub-boxes already searched in phase 1
+    const int own_sb0 = cbase / kSub, own_sb1 = own_sb0 + B / kSub;      // sub-boxes already searched in phase 1
 
     // ---- phase 2: 1024-point boxes -> their sub-boxes -> points
-    for (int c0 = 0; c0 < nb; c0 += 256) {
+    for (int c0 = 0; c0 < nb; c0 += B) {
         __syncthreads();
         if (tid == 0) s_n1 = 0;
         __syncthreads();
@@ -248,7 +252,7 @@ __global__ void __launch_bounds__(256) knn_kernel(int P, const float4* __restric
         }
         __syncthreads();
         const int n1 = s_n1;
-        for (int g0 = 0; g0 < n1; g0 += 256 / kSubPerBox) {              // 16 boxes -> 256 sub-boxes, one per thread
+        for (int g0 = 0; g0 < n1; g0 += B / kSubPerBox) {                // B / 16 boxes -> B sub-boxes, one per thread
             __syncthreads();
             if (tid == 0) s_n0 = 0;
             __syncthreads();
@@ -306,7 +310,12 @@ int launch_dist2(int P, const float* pts, float* out, char* temp, cudaStream_t s
     const int nb = (P + kBox - 1) / kBox, nsub = (P + kSub - 1) / kSub;
     GSR_LAUNCH("knn_subboxes", false, s, (sub_minmax_kernel<<<(nsub + 7) / 8, 256, 0, s>>>(P, t.sorted, t.sub)));
     GSR_LAUNCH("knn_boxes", false, s, (box_from_sub_kernel<<<(nb + 255) / 256, 256, 0, s>>>(nb, nsub, t.sub, t.boxes)));
-    GSR_LAUNCH("knn_search", false, s, (knn_kernel<<<blocks, 256, 0, s>>>(P, t.sorted, t.boxes, nb, t.sub, nsub, out)));
+    int sms = 148;
+    { const int se = sm_count(&sms); if (se) return se; }
+    if (blocks < 2 * sms)                                           // small cloud: more, smaller CTAs (see knn_kernel)
+        GSR_LAUNCH("knn_search", false, s, (knn_kernel<64><<<(P + 63) / 64, 64, 0, s>>>(P, t.sorted, t.boxes, nb, t.sub, nsub, out)));
+    else
+        GSR_LAUNCH("knn_search", false, s, (knn_kernel<256><<<blocks, 256, 0, s>>>(P, t.sorted, t.boxes, nb, t.sub, nsub, out)));
     return 0;
 }
 

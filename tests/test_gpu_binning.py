@@ -241,3 +241,25 @@ def test_grad_sinks_overwrite_on_the_first_view_then_accumulate(binding):
             assert rel_l2(sinks[n].cpu().numpy(), want[n].cpu().numpy()) <= 1e-5, n
     finally:
         _C._ext = ext
+
+
+def test_split_forward_is_bit_identical_to_the_one_stream_forward():
+    """gsr_debug_set_split_forward(1): geometry pass + colour pass on different streams, binning chain on a high-priority
+    stream (an experiment kept behind a switch). Same kernels' arithmetic: state, image and gradients must not change."""
+    from diff_gaussian_rasterization import _C
+    L = _C.lib()
+    sc = _scene(20000, 0.02, 0.25)                       # > 12288: the multi-launch depth sort on the chain stream
+    cam = scenes.look_at_camera(480, 272, math.radians(65), (0.1, -0.2, -3.3))
+    dpix = np.random.default_rng(3).standard_normal((3, cam.H, cam.W)).astype(np.float32)
+    try:
+        L.gsr_debug_set_split_forward(0)
+        _run_ours(sc, cam, (0.2, 0.3, 0.1), dpix=dpix)                    # seeds the capacity estimate
+        plain = _run_ours(sc, cam, (0.2, 0.3, 0.1), dpix=dpix)
+        L.gsr_debug_set_split_forward(1)
+        split = [_run_ours(sc, cam, (0.2, 0.3, 0.1), dpix=dpix) for _ in range(3)]
+    finally:
+        L.gsr_debug_set_split_forward(0)
+    for s in split:
+        _same_state(plain, s)
+        for k in plain["grads"]:
+            assert rel_l2(s["grads"][k], plain["grads"][k]) <= 1e-5, k
