@@ -5,5 +5,5 @@ CMD="python bench.py --steps 1 --warmup 3 --no-extras --no-cpu-baseline --no-e2e
 $CMD > gpurun_out/ncu_plain_run.json 2> gpurun_out/ncu_plain_run.err; rc=$?; echo "plain rc=$rc"
 if [ $rc -ne 0 ]; then exit 86; fi
 # skip the warm-up (3 steps x 8 views x ~14 launches) and take the next 16 launches of the library's kernels
-ncu --set full --clock-control none --import-source on -k regex:'blend|preprocess|onesweep|emit_inst|scan_offsets|tile_table|radix_hist' --launch-skip 350 -c 14 -f -o gpurun_out/r02_full $CMD > gpurun_out/ncu_full_run.log 2>&1; echo "ncu rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:'blend|preprocess|onesweep|emit_inst|scan_|tile_table|radix_hist' --launch-skip 375 -c 15 -f -o gpurun_out/r02_full $CMD > gpurun_out/ncu_full_run.log 2>&1; echo "ncu rc=$?"
 ls -la gpurun_out/r02_full.ncu-rep

@@ -16,7 +16,8 @@ def short(name):
     m = re.search(r"(\w+)_kernel", name)
     if m:
         k = m.group(1)
-        return {"blend_backward_streams": "blend_backward", "blend_forward_streams": "blend_forward"}.get(k, k)
+        return {"blend_backward_streams": "blend_backward", "blend_forward_streams": "blend_forward",
+                "scan_apply_sums": "scan_offsets"}.get(k, k)
     return re.sub(r"\(.*", "", name).split("::")[-1][:40]
 
 # ---- launch list: share of the captured window per kernel
@@ -74,12 +75,12 @@ for row in data:
         k = "onesweep_depth" if seen_onesweep < 4 else "onesweep_tile"
     summary.setdefault(k, []).append(e)
     traffic[k].append(e.get("dram_read_bytes", 0) + e.get("dram_write_bytes", 0))
-json.dump({"command": "ncu --set full --clock-control none --import-source on -k regex:... --launch-skip 350 -c 14 python bench.py --steps 1 "
-                      "--warmup 3 ... (tools/gpu_ncu_full.sh: the 14 launches of one 3M-Gaussian 1080p view of the timed step)",
+json.dump({"command": "ncu --set full --clock-control none --import-source on -k regex:... --launch-skip 375 -c 15 python bench.py --steps 1 "
+                      "--warmup 3 ... (tools/gpu_ncu_full.sh: the 15 launches of one 3M-Gaussian 1080p view of the timed step)",
            "kernels": summary}, open(os.path.join(out_dir, f"{tag}_ncu_full_summary.json"), "w"), indent=1)
 # bench.py names (per-launch DRAM bytes, mean over the captured launches of that kernel)
 name_map = {k: k for k in ("blend_forward", "blend_backward", "preprocess_fwd", "preprocess_bwd", "emit_instances",
-                           "onesweep_depth", "onesweep_tile", "radix_hist", "tile_table", "scan_offsets")}
+                           "onesweep_depth", "onesweep_tile", "radix_hist", "tile_table", "scan_offsets", "scan_tile_sums")}
 tr = {name_map[k]: round(sum(v) / len(v)) for k, v in traffic.items() if k in name_map}
 json.dump(tr, open(os.path.join(out_dir, "ncu_traffic.json"), "w"), indent=1)
 print(json.dumps(share, indent=1)); print(json.dumps(tr))
