@@ -292,16 +292,20 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_sums_kernel(const uin
     }
 }
 
-// Replaces duplicateWithKeys (rasterizer_impl.cu:70-111), balanced by OUTPUT: a CTA writes 4096 consecutive instance
+// Replaces duplicateWithKeys (rasterizer_impl.cu:70-111), balanced by OUTPUT: a CTA writes kEmitTile (2048) consecutive instance
 // slots, whatever number of Gaussians they belong to. (Emitting per Gaussian -- the reference's mapping, one thread per
 // Gaussian -- leaves the near Gaussians, which cover hundreds of tiles each and come first in depth order, to a few
 // threads while the rest of the GPU idles.) The CTA finds the Gaussians that own its slots in two cooperative steps,
 // both counts over sorted arrays: the scan's per-tile inclusive prefixes give the first and last scan tile, the offsets
-// of those two tiles the first and last Gaussian. Their offsets / ids / rectangles (<= 4097 of each) are staged in shared
+// of those two tiles the first and last Gaussian. Their offsets / ids / rectangles (<= kEmitTile + 1 of each) are staged in shared
 // memory; a slot's owner is the number of range ends at or before it: the ends are strictly increasing, so they are
-// distinct bits of a 4096-bit map, and the owner is a prefix popcount. Stores are coalesced, writes clamped to `cap`.
+// distinct bits of a kEmitTile-bit map, and the owner is a prefix popcount. Stores are coalesced, writes clamped to `cap`.
 constexpr int kEmitThreads = 256;
-constexpr int kEmitTile = 4096;                             // slots per CTA
+#ifndef GSR_EMIT_TILE
+#define GSR_EMIT_TILE 2048
+#endif
+constexpr int kEmitTile = GSR_EMIT_TILE;                    // slots per CTA (a multiple of 1024). Measured at C3: 4096 -> 0.0597 ms,
+                                                            // 2048 -> 0.0570 ms (twice the CTAs resident hide the search latency), 1024 -> 0.0782 ms
 constexpr int kEmitMax = kEmitTile + 8;                     // Gaussians a CTA can need (4097), padded
 template <bool PACKED>
 __global__ void __launch_bounds__(kEmitThreads) emit_instances_kernel(const uint32_t* __restrict__ n_dev,
@@ -381,10 +385,11 @@ __global__ void __launch_bounds__(kEmitThreads) emit_instances_kernel(const uint
         if (rel < (uint32_t)kEmitTile) atomicOr(&s_bits[rel >> 5], 1u << (rel & 31u));
     }
     __syncthreads();
-    if (t < 32) {                                           // exclusive prefix of the words' popcounts (128 words: 4 per lane)
-        uint32_t c4[4], sum = 0;
+    if (t < 32) {                                           // exclusive prefix of the words' popcounts (kEmitTile / 1024 words per lane)
+        constexpr int kW = kEmitTile / 32 / 32;
+        uint32_t c4[kW], sum = 0;
 #pragma unroll
-        for (int q = 0; q < 4; q++) { c4[q] = __popc(s_bits[4 * t + q]); sum += c4[q]; }
+        for (int q = 0; q < kW; q++) { c4[q] = __popc(s_bits[kW * t + q]); sum += c4[q]; }
         uint32_t incl = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -393,7 +398,7 @@ __global__ void __launch_bounds__(kEmitThreads) emit_instances_kernel(const uint
         }
         uint32_t run = incl - sum;
 #pragma unroll
-        for (int q = 0; q < 4; q++) { s_wpre[4 * t + q] = run; run += c4[q]; }
+        for (int q = 0; q < kW; q++) { s_wpre[kW * t + q] = run; run += c4[q]; }
     }
     __syncthreads();
 #pragma unroll 4
