@@ -53,7 +53,7 @@ __device__ __forceinline__ void rect_of(float px, float py, int max_radius, int 
 }
 
 // Replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:277): single-pass chained scan (decoupled look-back) of
-// the tile counts in DEPTH order. CTA b takes the b-th 2048 visible Gaussians, gathers their packed rectangles through
+// the tile counts in DEPTH order. CTA b takes the b-th GSR_SCAN_TILE visible Gaussians, gathers their packed rectangles through
 // `order` (L2 hits: 4 B x P), scans locally, publishes its sum and looks back with ALL its threads (1024 predecessors per round trip). A tile's
 // status word carries flag (bits 30-31: 1 = the tile's own sum, 2 = inclusive prefix) and value (30 bits, saturating)
 // together, so one 32-bit store publishes both. status[0..m) = tile words (all inclusive prefixes once the kernel has
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_tile_sums_kernel(const uint
         uint32_t tot = 0;
 #pragma unroll
         for (int k = 0; k < kScanThreads / 32; k++) tot += warp_sums[k];
-        sums[tile] = tot;                                  // <= 2048 * 255 * 255: fits
+        sums[tile] = tot;                                  // <= GSR_SCAN_TILE * 255 * 255: fits
     }
 }
 

@@ -87,7 +87,10 @@ static inline T* carve(char*& p, size_t count) {
 #define GSR_SORT_TILE 4096    // keys per radix-sort tile (256 threads x 16)
 #endif
 #define GSR_RADIX 256
-#define GSR_SCAN_TILE 2048    // items per scan tile (256 threads x 8): 3M Gaussians, half of them visible -> one wave of CTAs
+#ifndef GSR_SCAN_TILE
+#define GSR_SCAN_TILE 1024    // items per scan tile (256 threads x 4). Measured at C3 (scan pass 2 + emission, whose second search
+                              // level walks two scan tiles): 4096 -> 0.086 ms, 2048 -> 0.071 ms, 1024 -> 0.063 ms
+#endif
 
 static inline size_t sort_tiles(size_t n) { return (n + GSR_SORT_TILE - 1) / GSR_SORT_TILE; }
 // scratch words for radix_sort_u32 over n items: digit histograms [4][256], tickets, and one look-back status
