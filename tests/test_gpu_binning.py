@@ -263,3 +263,26 @@ def test_split_forward_is_bit_identical_to_the_one_stream_forward():
         _same_state(plain, s)
         for k in plain["grads"]:
             assert rel_l2(s["grads"][k], plain["grads"][k]) <= 1e-5, k
+
+
+def test_forward_without_the_side_stream_and_with_nvtx_ranges_is_unchanged():
+    """gsr_set_speculation(2) keeps the speculative capacity but runs the tile table in-stream; gsr_nvtx_enable(1) wraps
+    every launch in an NVTX range. Neither may change a bit of the result."""
+    from diff_gaussian_rasterization import _C
+    L = _C.lib()
+    sc = _scene(5000, 0.02, 0.25)
+    cam = scenes.look_at_camera(320, 208, math.radians(65), (0.1, -0.2, -3.3))
+    try:
+        _C.set_speculation(True)
+        _run_ours(sc, cam, (0.2, 0.3, 0.1))                               # seeds the capacity estimate
+        plain = _run_ours(sc, cam, (0.2, 0.3, 0.1))
+        L.gsr_set_speculation(2)
+        in_stream = _run_ours(sc, cam, (0.2, 0.3, 0.1))
+        L.gsr_set_speculation(1)
+        L.gsr_nvtx_enable(1)
+        ranged = _run_ours(sc, cam, (0.2, 0.3, 0.1))
+    finally:
+        L.gsr_nvtx_enable(0)
+        L.gsr_set_speculation(1)
+    _same_state(plain, in_stream)
+    _same_state(plain, ranged)
