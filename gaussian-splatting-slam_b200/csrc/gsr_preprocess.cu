@@ -188,11 +188,14 @@ struct PreArgs {
     uint32_t* zero_b; long long zero_b_words;
 };
 
+#ifndef GSR_PFWD_CTAS
+#define GSR_PFWD_CTAS 3           // (x 256 threads; CTAs are 128 threads) 85 registers: 0.130 ms against 0.131 at 4, 0.172 at 5
+#endif
 // GEOM_ONLY: the colour (SH evaluation, the 192-byte row per visible Gaussian) and the clamp bits are left to
 // preprocess_color_kernel, which gsr_forward runs on a side stream UNDER the latency-bound depth sort / scan / instance
 // sort: nothing before the blend needs the colours, and they are 60 % of this kernel's bytes.
 template <bool SH16, bool GEOM_ONLY>
-__global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(const PreArgs a, int* __restrict__ radii,
+__global__ void __launch_bounds__(256, GSR_PFWD_CTAS) preprocess_fwd_kernel(const PreArgs a, int* __restrict__ radii,
                                                               float* __restrict__ depths, float4* __restrict__ rec,
                                                               float4* __restrict__ colr,
                                                               uint8_t* __restrict__ clamped,
@@ -388,8 +391,14 @@ struct PreBwdArgs {
     gsr_grads out;
 };
 
+#ifndef GSR_PBWD_CTAS
+#define GSR_PBWD_CTAS 3           // 3 x 256 threads at 85 registers (no spills): 0.298 ms against 0.304 at 4 x 64 registers
+#endif
+#ifndef GSR_PBWD_KU
+#define GSR_PBWD_KU 4
+#endif
 template <bool SH16>
-__global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs b) {
+__global__ void __launch_bounds__(256, GSR_PBWD_CTAS) preprocess_bwd_kernel(const PreBwdArgs b) {
     const PreArgs& a = b.f;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const bool inside = idx < a.P;
@@ -770,7 +779,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(const PreBwdArgs
         const int nq = accum ? n_quads : 12;
         float* dst0 = o.dL_dsh + (size_t)blockIdx.x * 256 * 48;
         const int total = n_vis * nq;
-        constexpr int kU = 4;                          // old rows: kU 16-byte loads in flight per thread before any store
+        constexpr int kU = GSR_PBWD_KU;                // old rows: kU 16-byte loads in flight per thread before any store
         for (int f0 = threadIdx.x; f0 < total; f0 += 256 * kU) {
             float4* d[kU];
             float4 c[kU], v[kU];

@@ -22,7 +22,10 @@ namespace gsr {
 
 constexpr int kSortThreads = 256;
 constexpr int kSortItems = GSR_SORT_TILE / kSortThreads;   // 16
-constexpr int kSortCtasPerSm = GSR_SORT_TILE >= 4096 ? 3 : 5;
+#ifndef GSR_SORT_CTAS
+#define GSR_SORT_CTAS (GSR_SORT_TILE >= 4096 ? 3 : 5)
+#endif
+constexpr int kSortCtasPerSm = GSR_SORT_CTAS;
 constexpr int kSortWarps = kSortThreads / 32;               // 8
 constexpr uint32_t kFlagAgg = 1u << 30, kFlagInc = 2u << 30, kValMask = (1u << 30) - 1u;
 constexpr unsigned kAll = 0xffffffffu;
