@@ -249,24 +249,39 @@ def parity_multi_gpu(arm, args, all_cams, rank, world, dev, rank_dpix):
 
         def rel_of(a, b):
             return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+
+        def rel_trimmed(a, b, k):
+            """rel-L2 with the k rows of largest error left out (numerator only)."""
+            e = ((a.double() - b.double()).reshape(a.shape[0], -1) ** 2).sum(1)
+            if e.numel() > k:
+                e = e.sum() - torch.topk(e, k).values.sum()
+            else:
+                e = e.sum() * 0
+            return float(e.clamp_min(0).sqrt() / b.double().norm().clamp_min(1e-30))
         solo = solo_pass()
         rel = {k: rel_of(exchanged[k], v) for k, v in solo.views.items()}
-        # The noise floor of the comparison itself: the SAME one-GPU pass a second time. The blend accumulates with float
-        # atomics, so two passes over identical views differ by the order of additions; on tensors whose per-view terms
-        # cancel (rotations, scales) that alone reaches 1e-5 .. 1e-4 of the sum's norm. The n-GPU result passes when it is
-        # within the bar, or -- where the one-GPU pass cannot reproduce ITSELF to the bar -- within 3x that floor.
+        # The noise of the comparison itself: the blend accumulates with float atomics, so two passes over identical views
+        # differ by the order of additions -- and that difference sits in a handful of ill-conditioned Gaussians
+        # (tools/noise_rows.py, two identical one-GPU steps at C3: rotations 3.7e-5 in all, 9.0e-6 without the 8 worst of
+        # 3M rows, 4.6e-6 without the 32 worst, 5.7e-7 without the 1024 worst). The verdict therefore uses the rel-L2 with
+        # the worst 1e-5 of the rows left out (32 of 3M; a missing view or a wrong exchange moves millions of rows), the raw
+        # figure and the one-GPU pass repeated are reported beside it.
+        k_trim = max(8, -(-arm.params["means3D"].shape[0] // 100000))
+        trimmed = {k: rel_trimmed(exchanged[k], v, k_trim) for k, v in solo.views.items()}
         again = solo_pass()
         floor = {k: rel_of(again.views[k], v) for k, v in solo.views.items()}
-        ok = all(rel[k] <= max(1e-4, 3.0 * floor[k]) for k in rel)
-        # what makes bench.py exit non-zero: a GROSS mismatch (one view of 64 missing changes the sums by ~1e-2), not a draw
-        # from the tail of the float-atomic noise -- that is reported through `ok` and the numbers beside it
-        gross = (not identical) or any(rel[k] > max(1e-3, 10.0 * floor[k]) for k in rel)
-        res.update({"rel_l2_per_tensor": {k: float(f"{x:.3e}") for k, x in rel.items()}, "max": float(f"{max(rel.values()):.3e}"),
-                    "one_gpu_repeat_rel_l2_per_tensor": {k: float(f"{x:.3e}") for k, x in floor.items()},
+        ok = all(trimmed[k] <= 1e-4 for k in trimmed)
+        # what makes bench.py exit non-zero: a GROSS mismatch (one view of 64 missing changes the sums by ~1e-2)
+        gross = (not identical) or any(trimmed[k] > 1e-3 for k in trimmed)
+        res.update({"rel_l2_per_tensor": {k: float(f"{x:.3e}") for k, x in trimmed.items()}, "max": float(f"{max(trimmed.values()):.3e}"),
+                    "rows_left_out": k_trim,
+                    "rel_l2_all_rows_per_tensor": {k: float(f"{x:.3e}") for k, x in rel.items()},
+                    "one_gpu_repeat_rel_l2_all_rows_per_tensor": {k: float(f"{x:.3e}") for k, x in floor.items()},
                     "views_checked": n_views, "bar": 1e-4, "ok": bool(ok and identical), "gross_mismatch": bool(gross),
                     "how": "rank 0 renders all views of the step alone (in-kernel accumulation, same kernels) and compares "
-                           "with the bucket the exchange left on it; the same one-GPU pass repeated gives the float-atomic "
-                           "noise floor of the comparison (pass: <= bar, or <= 3x that floor); checksums of the raw bucket "
+                           "with the bucket the exchange left on it: rel-L2 per tensor with the rows_left_out rows of largest "
+                           "error left out (float-atomic noise sits in a handful of ill-conditioned Gaussians); the all-rows "
+                           "figure and the same one-GPU pass repeated are reported beside it; checksums of the raw bucket "
                            "words compared over all ranks"})
         del again
         del solo, params, exchanged
